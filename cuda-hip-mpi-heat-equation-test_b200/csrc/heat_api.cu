@@ -1,0 +1,620 @@
+// heat_api.cu — the C ABI of libheat.so (include/heat_b200.h): handle, buffers, streams, kernel
+// dispatch, row-slab halo exchange.  B200 (sm_100a) only; there is no CPU fallback anywhere: without
+// a CUDA device heat_init fails with HEAT_ERR_CUDA.
+#include "../../include/heat_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "kernels_basic.cuh"
+#include "kernels_tma.cuh"
+#include "nccl_dyn.h"
+
+using namespace heat;
+
+// ------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t e_ = (expr);                                                                \
+        if (e_ != cudaSuccess)                                                                  \
+            return fail(HEAT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_),  \
+                        __FILE__, __LINE__);                                                    \
+    } while (0)
+
+#define NCCL_TRY(expr)                                                                          \
+    do {                                                                                        \
+        ncclResult_t r_ = (expr);                                                               \
+        if (r_ != 0)                                                                            \
+            return fail(HEAT_ERR_NCCL, "%s failed: %s (%s:%d)", #expr,                          \
+                        nccl_api().GetErrorString(r_), __FILE__, __LINE__);                     \
+    } while (0)
+
+// ------------------------------------------------------------------------------------ handle
+struct heat_handle {
+    heat_config cfg{};
+    int dev = 0;
+    int nx = 0, ny = 0;            // global
+    int row0 = 0, nrows = 0;       // owned global rows
+    int g = 0;                     // ghost depth (0 when nranks == 1)
+    int lrows = 0;                 // nrows + 2g
+    long pitch = 0;                // elements
+    size_t esize = 8;
+    void* buf[2] = {nullptr, nullptr};
+    bool owns = false;
+    int cur = 0;
+    int kernel = HEAT_KERNEL_SIMPLE;
+    int tblock = 1;
+    bool fma = false;
+    int valid_ghost = 0;           // ghost rows of buf[cur] that hold current-time values
+    bool comm_pending = false;     // an exchange is in flight on s_comm
+    cudaStream_t s_compute = nullptr, s_comm = nullptr;
+    bool owns_stream = false;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_boundary = nullptr, ev_comm = nullptr,
+                ev_h0 = nullptr, ev_h1 = nullptr;
+    bool timed = false, halo_timed = false;
+    ncclComm_t comm = nullptr;
+    double* d_partials = nullptr;  // checksum scratch (lazily allocated)
+    double* d_sum = nullptr;
+    void* d_stage = nullptr;       // global-gather staging on the root (lazily allocated)
+    size_t stage_bytes = 0;
+    TmaState tma;                  // tensor maps for the TMA kernels (kernels_tma.cuh)
+    int sm_count = 148;
+    int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
+    uint64_t steps_total = 0, launches = 0, exchanges = 0;
+};
+
+static const int kSumBlocks = 592;   // 148 SMs x 4; fixed so the checksum's reduction tree is fixed
+
+static inline size_t row_bytes(const heat_handle* h) { return (size_t)h->pitch * h->esize; }
+static inline char* row_ptr(const heat_handle* h, int which, int lrow) {
+    return (char*)h->buf[which] + (size_t)lrow * row_bytes(h);
+}
+// local row index of a global row
+static inline int lrow(const heat_handle* h, int grow) { return grow - h->row0 + h->g; }
+
+// ------------------------------------------------------------------------------------ dispatch
+template <typename T, int ORDER, bool FMA>
+static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int yb, int ye,
+                                 cudaStream_t s) {
+    if (yb >= ye || h->nx < 3) return cudaSuccess;
+    const T rx = (T)h->cfg.rx, ry = (T)h->cfg.ry;
+    const T* S = (const T*)src;
+    T* D = (T*)dst;
+    const int rows = ye - yb;
+    h->launches++;
+    if (h->kernel == HEAT_KERNEL_STREAM) {
+        constexpr int V = Pack<T>::V;
+        const int threads = h->stream_threads ? h->stream_threads : 256;
+        const long nvec = h->pitch / V;
+        const int gx = (int)((nvec + threads - 1) / threads);
+        int rpb = h->stream_rows;
+        if (rpb <= 0) {
+            const int target_blocks = h->sm_count * 16;
+            const int ychunks = std::max(1, target_blocks / gx);
+            rpb = std::max(32, (rows + ychunks - 1) / ychunks);
+        }
+        rpb = std::min(rpb, rows);
+        const int gy = (rows + rpb - 1) / rpb;
+        heat_stream_kernel<T, ORDER, FMA, 4><<<dim3(gx, gy), threads, 0, s>>>(
+            S, D, h->nx, h->pitch, yb, ye, rpb, rx, ry);
+    } else if (h->kernel == HEAT_KERNEL_TMA) {
+        return launch_tma_rows<T, ORDER, FMA>(h->tma, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch,
+                                              yb, ye, rx, ry, h->sm_count, s);
+    } else {
+        dim3 block(32, 8);
+        dim3 grid((h->nx - 2 + 31) / 32, (rows + 7) / 8);
+        heat_simple_kernel<T, ORDER, FMA><<<grid, block, 0, s>>>(S, D, h->nx, h->pitch, yb, ye, rx, ry);
+    }
+    return cudaGetLastError();
+}
+
+template <typename T, int ORDER, bool FMA>
+static cudaError_t launch_resident_t(heat_handle* h, const void* src, void* dst, int nt, cudaStream_t s) {
+    const size_t smem = 2 * (size_t)h->nx * h->ny * sizeof(T);
+    auto k = heat_resident_kernel<T, ORDER, FMA>;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int cells = h->nx * h->ny;
+    const int threads = std::min(1024, std::max(32, ((cells + 31) / 32) * 32));
+    h->launches++;
+    k<<<1, threads, smem, s>>>((const T*)src, (T*)dst, h->nx, h->ny, h->pitch, nt, (T)h->cfg.rx, (T)h->cfg.ry);
+    return cudaGetLastError();
+}
+
+#define HEAT_DISPATCH(h, FN, ...)                                                                   \
+    [&]() -> cudaError_t {                                                                          \
+        const int key_ = ((h)->cfg.dtype == HEAT_F32 ? 6 : 0) + (h)->cfg.op_order * 2 + ((h)->fma ? 1 : 0); \
+        switch (key_) {                                                                             \
+            case 0: return FN<double, 0, false>(__VA_ARGS__);                                       \
+            case 1: return FN<double, 0, true>(__VA_ARGS__);                                        \
+            case 2: return FN<double, 1, false>(__VA_ARGS__);                                       \
+            case 3: return FN<double, 1, true>(__VA_ARGS__);                                        \
+            case 4: return FN<double, 2, false>(__VA_ARGS__);                                       \
+            case 5: return FN<double, 2, true>(__VA_ARGS__);                                        \
+            case 6: return FN<float, 0, false>(__VA_ARGS__);                                        \
+            case 7: return FN<float, 0, true>(__VA_ARGS__);                                         \
+            case 8: return FN<float, 1, false>(__VA_ARGS__);                                        \
+            case 9: return FN<float, 1, true>(__VA_ARGS__);                                         \
+            case 10: return FN<float, 2, false>(__VA_ARGS__);                                       \
+            case 11: return FN<float, 2, true>(__VA_ARGS__);                                        \
+        }                                                                                           \
+        return cudaErrorInvalidValue;                                                               \
+    }()
+
+// update global rows [glo, ghi] (inclusive) of buf[cur] -> buf[cur^1]
+static cudaError_t update_rows(heat_handle* h, int glo, int ghi, cudaStream_t s) {
+    glo = std::max(glo, 1);
+    ghi = std::min(ghi, h->ny - 2);
+    if (glo > ghi) return cudaSuccess;
+    const void* src = h->buf[h->cur];
+    void* dst = h->buf[h->cur ^ 1];
+    const int yb = lrow(h, glo), ye = lrow(h, ghi) + 1;
+    return HEAT_DISPATCH(h, launch_rows_t, h, src, dst, yb, ye, s);
+}
+
+// ------------------------------------------------------------------------------------ halo exchange
+// Row slabs along the slow index make every halo a contiguous block of g rows, so NCCL reads the
+// field rows and writes the neighbour's ghost rows directly: no pack/unpack kernels and no staging
+// (contrast fortran/mpi+cuda/heat.F90:153-159,163-168,175-190).
+static int exchange(heat_handle* h, int which, cudaStream_t s) {
+    if (h->cfg.nranks <= 1) return HEAT_OK;
+    h->exchanges++;
+    if (h->cfg.flags & HEAT_FLAG_SKIP_EXCHANGE) return HEAT_OK;
+    const NcclApi& N = nccl_api();
+    const size_t count = (size_t)h->g * h->pitch;
+    const int dt = h->cfg.dtype == HEAT_F32 ? ncclFloat32 : ncclFloat64;
+    const int up = h->cfg.rank - 1, down = h->cfg.rank + 1;
+    CUDA_TRY(cudaEventRecord(h->ev_h0, s));
+    NCCL_TRY(N.GroupStart());
+    if (up >= 0) {
+        NCCL_TRY(N.Send(row_ptr(h, which, h->g), count, dt, up, h->comm, s));
+        NCCL_TRY(N.Recv(row_ptr(h, which, 0), count, dt, up, h->comm, s));
+    }
+    if (down < h->cfg.nranks) {
+        NCCL_TRY(N.Send(row_ptr(h, which, h->nrows), count, dt, down, h->comm, s));
+        NCCL_TRY(N.Recv(row_ptr(h, which, h->g + h->nrows), count, dt, down, h->comm, s));
+    }
+    NCCL_TRY(N.GroupEnd());
+    CUDA_TRY(cudaEventRecord(h->ev_h1, s));
+    h->halo_timed = true;
+    return HEAT_OK;
+}
+
+static int wait_comm(heat_handle* h) {
+    if (h->comm_pending) {
+        CUDA_TRY(cudaStreamWaitEvent(h->s_compute, h->ev_comm, 0));
+        h->comm_pending = false;
+    }
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------------------------ helpers
+static int resolve_kernel(heat_handle* h) {
+    const heat_config& c = h->cfg;
+    const size_t V = 16 / h->esize;
+    const bool aligned = (h->pitch % (long)V == 0) && ((uintptr_t)h->buf[0] % 16 == 0) &&
+                         ((uintptr_t)h->buf[1] % 16 == 0);
+    const bool fits_resident = c.nranks == 1 && h->nx >= 3 && h->ny >= 3 &&
+                               2 * (size_t)h->nx * h->ny * h->esize <= 200 * 1024;
+    int k = c.kernel;
+    if (k == HEAT_KERNEL_AUTO) {
+        if (fits_resident) k = HEAT_KERNEL_RESIDENT;
+        else if (aligned) k = HEAT_KERNEL_STREAM;
+        else k = HEAT_KERNEL_SIMPLE;
+    }
+    if (k == HEAT_KERNEL_RESIDENT && !fits_resident)
+        return fail(HEAT_ERR_UNSUPPORTED, "RESIDENT kernel needs nranks == 1 and 2*nx*ny*sizeof(T) <= 200 KiB");
+    if ((k == HEAT_KERNEL_STREAM || k == HEAT_KERNEL_TMA) && !aligned)
+        return fail(HEAT_ERR_UNSUPPORTED, "STREAM/TMA kernels need 16-byte aligned buffers and a pitch that is a multiple of %d elements", (int)V);
+    if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_RESIDENT) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
+    h->kernel = k;
+    return HEAT_OK;
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// ------------------------------------------------------------------------------------ C ABI
+extern "C" {
+
+const char* heat_last_error(void) { return g_err.c_str(); }
+const char* heat_version(void) { return "heat_b200 0.1 (sm_100a)"; }
+
+int heat_slab_partition(int ny, int nranks, int rank, int* row0, int* nrows) {
+    if (ny < 1 || nranks < 1 || rank < 0 || rank >= nranks || !row0 || !nrows)
+        return fail(HEAT_ERR_INVALID, "heat_slab_partition: bad arguments (ny=%d nranks=%d rank=%d)", ny, nranks, rank);
+    const int base = ny / nranks, rem = ny % nranks;
+    *nrows = base + (rank < rem ? 1 : 0);
+    *row0 = rank * base + std::min(rank, rem);
+    return HEAT_OK;
+}
+
+int heat_derive_fortran(int n, double sigma, double nu, double dom_len, double* delta, double* dt, double* r) {
+    if (n < 2 || !delta || !dt || !r) return fail(HEAT_ERR_INVALID, "heat_derive_fortran: bad arguments");
+    // ref: fortran/serial/heat.f90:15,17,59 — real(n-1) is a default (fp32) real; delta**2 = delta*delta
+    volatile double d = dom_len / (double)(float)(n - 1);
+    volatile double d2 = d * d;
+    volatile double sd = sigma * d2;
+    volatile double t = sd / nu;
+    volatile double nt = nu * t;
+    *delta = d;
+    *dt = t;
+    *r = nt / d2;
+    return HEAT_OK;
+}
+
+int heat_nccl_unique_id(void* out128) {
+    if (!out128) return fail(HEAT_ERR_INVALID, "heat_nccl_unique_id: null output");
+    const NcclApi& N = nccl_api();
+    if (!N.ok) return fail(HEAT_ERR_NCCL, "NCCL not available: %s", dlerror() ? dlerror() : "libnccl.so.2 not found");
+    ncclUniqueId id;
+    NCCL_TRY(N.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof id);
+    return HEAT_OK;
+}
+
+int heat_destroy(heat_handle* h) {
+    if (!h) return HEAT_OK;
+    cudaSetDevice(h->dev);
+    if (h->s_compute) cudaStreamSynchronize(h->s_compute);
+    if (h->s_comm) cudaStreamSynchronize(h->s_comm);
+    if (h->comm) nccl_api().CommDestroy(h->comm);
+    if (h->owns) { cudaFree(h->buf[0]); cudaFree(h->buf[1]); }
+    cudaFree(h->d_partials);
+    cudaFree(h->d_sum);
+    cudaFree(h->d_stage);
+    for (cudaEvent_t e : {h->ev_t0, h->ev_t1, h->ev_boundary, h->ev_comm, h->ev_h0, h->ev_h1})
+        if (e) cudaEventDestroy(e);
+    if (h->s_comm) cudaStreamDestroy(h->s_comm);
+    if (h->owns_stream && h->s_compute) cudaStreamDestroy(h->s_compute);
+    delete h;
+    return HEAT_OK;
+}
+
+int heat_set_field(heat_handle* h, const void* src, int64_t src_pitch, int src_is_device) {
+    if (!h || !src) return fail(HEAT_ERR_INVALID, "heat_set_field: null argument");
+    if (src_pitch <= 0) src_pitch = h->nx;
+    if (src_pitch < h->nx) return fail(HEAT_ERR_INVALID, "heat_set_field: src_pitch %lld < nx %d", (long long)src_pitch, h->nx);
+    CUDA_TRY(cudaSetDevice(h->dev));
+    int rc = wait_comm(h);
+    if (rc) return rc;
+    const cudaMemcpyKind kind = src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    // one trip over PCIe into buffer 0, then a device-side copy into buffer 1 (both need the Dirichlet ring)
+    CUDA_TRY(cudaMemcpy2DAsync(row_ptr(h, 0, h->g), row_bytes(h), src, (size_t)src_pitch * h->esize,
+                               (size_t)h->nx * h->esize, h->nrows, kind, h->s_compute));
+    CUDA_TRY(cudaMemcpyAsync(row_ptr(h, 1, h->g), row_ptr(h, 0, h->g), (size_t)h->nrows * row_bytes(h),
+                             cudaMemcpyDeviceToDevice, h->s_compute));
+    h->cur = 0;
+    h->valid_ghost = 0;
+    if (h->cfg.nranks > 1) {
+        // fill both buffers' ghosts so that the Dirichlet/ghost rows agree in both (collective)
+        for (int b = 0; b < 2; ++b) {
+            rc = exchange(h, b, h->s_compute);
+            if (rc) return rc;
+        }
+        h->valid_ghost = h->g;
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    return HEAT_OK;
+}
+
+int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
+    if (!out || !cfg) return fail(HEAT_ERR_INVALID, "heat_init: null argument");
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(heat_config))
+        return fail(HEAT_ERR_INVALID, "heat_init: heat_config.struct_size is %u, this library expects %zu",
+                    cfg->struct_size, sizeof(heat_config));
+    if (cfg->nx < 1 || cfg->ny < 1) return fail(HEAT_ERR_INVALID, "heat_init: nx, ny must be >= 1 (got %d x %d)", cfg->nx, cfg->ny);
+    if (cfg->dtype != HEAT_F64 && cfg->dtype != HEAT_F32) return fail(HEAT_ERR_INVALID, "heat_init: bad dtype %d", cfg->dtype);
+    if (cfg->op_order < 0 || cfg->op_order > 2) return fail(HEAT_ERR_INVALID, "heat_init: bad op_order %d", cfg->op_order);
+    if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks)
+        return fail(HEAT_ERR_INVALID, "heat_init: bad rank %d of %d", cfg->rank, cfg->nranks);
+    if (cfg->tblock < 0 || cfg->tblock > 8) return fail(HEAT_ERR_INVALID, "heat_init: tblock must be in 0..8");
+    if (cfg->nranks > 1 && !cfg->nccl_id && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE))
+        return fail(HEAT_ERR_INVALID, "heat_init: nranks > 1 needs cfg.nccl_id");
+    if ((cfg->ext_buf[0] == nullptr) != (cfg->ext_buf[1] == nullptr))
+        return fail(HEAT_ERR_INVALID, "heat_init: supply both ext_buf pointers or neither");
+
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(HEAT_ERR_CUDA, "heat_init: no CUDA device (%s); libheat has no CPU path", cudaGetErrorString(ce));
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(HEAT_ERR_INVALID, "heat_init: device %d out of range (0..%d)", cfg->device, ndev - 1);
+
+    heat_handle* h = new (std::nothrow) heat_handle;
+    if (!h) return fail(HEAT_ERR_NOMEM, "heat_init: out of host memory");
+    h->cfg = *cfg;
+    h->dev = cfg->device;
+    h->nx = cfg->nx;
+    h->ny = cfg->ny;
+    h->esize = cfg->dtype == HEAT_F32 ? 4 : 8;
+    h->fma = (cfg->flags & HEAT_FLAG_FMAD) != 0;
+    h->tblock = cfg->tblock > 0 ? cfg->tblock : 1;
+    h->stream_rows = env_int("HEAT_STREAM_ROWS", 0);
+    h->stream_threads = env_int("HEAT_STREAM_THREADS", 0);
+    int rc = heat_slab_partition(h->ny, cfg->nranks, cfg->rank, &h->row0, &h->nrows);
+    if (rc) { delete h; return rc; }
+    h->g = cfg->nranks > 1 ? (cfg->ghost > 0 ? cfg->ghost : 1) : 0;
+    if (cfg->nranks > 1 && h->nrows < h->g) {
+        delete h;
+        return fail(HEAT_ERR_INVALID, "heat_init: slab of %d rows is thinner than ghost depth %d", h->nrows, h->g);
+    }
+    if (h->g % h->tblock != 0 && cfg->nranks > 1) {
+        delete h;
+        return fail(HEAT_ERR_INVALID, "heat_init: ghost depth %d must be a multiple of tblock %d", h->g, h->tblock);
+    }
+    h->lrows = h->nrows + 2 * h->g;
+
+#define INIT_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t e_ = (expr);                                                                \
+        if (e_ != cudaSuccess) {                                                                \
+            int c_ = fail(e_ == cudaErrorMemoryAllocation ? HEAT_ERR_NOMEM : HEAT_ERR_CUDA,     \
+                          "%s failed: %s", #expr, cudaGetErrorString(e_));                      \
+            std::string keep = g_err; heat_destroy(h); g_err = keep;                            \
+            return c_;                                                                          \
+        }                                                                                       \
+    } while (0)
+
+    INIT_TRY(cudaSetDevice(h->dev));
+    INIT_TRY(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->dev));
+    if (cfg->ext_buf[0]) {
+        h->buf[0] = cfg->ext_buf[0];
+        h->buf[1] = cfg->ext_buf[1];
+        h->pitch = cfg->ext_pitch > 0 ? cfg->ext_pitch : h->nx;
+        if (h->pitch < h->nx) { heat_destroy(h); return fail(HEAT_ERR_INVALID, "heat_init: ext_pitch < nx"); }
+        h->owns = false;
+    } else {
+        h->pitch = ((long)h->nx + 15) / 16 * 16;     // rows start on 128-byte (f64) / 64-byte (f32) boundaries
+        const size_t bytes = (size_t)h->lrows * row_bytes(h);
+        h->owns = true;
+        INIT_TRY(cudaMalloc(&h->buf[0], bytes));
+        INIT_TRY(cudaMalloc(&h->buf[1], bytes));
+        INIT_TRY(cudaMemset(h->buf[0], 0, bytes));
+        INIT_TRY(cudaMemset(h->buf[1], 0, bytes));
+    }
+    if (cfg->stream) {
+        h->s_compute = (cudaStream_t)(uintptr_t)cfg->stream;
+    } else {
+        INIT_TRY(cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking));
+        h->owns_stream = true;
+    }
+    int prio_lo = 0, prio_hi = 0;
+    INIT_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    INIT_TRY(cudaStreamCreateWithPriority(&h->s_comm, cudaStreamNonBlocking, prio_hi));
+    for (cudaEvent_t* e : {&h->ev_t0, &h->ev_t1, &h->ev_h0, &h->ev_h1}) INIT_TRY(cudaEventCreate(e));
+    for (cudaEvent_t* e : {&h->ev_boundary, &h->ev_comm}) INIT_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+
+    rc = resolve_kernel(h);
+    if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
+    if (h->kernel == HEAT_KERNEL_TMA) {
+        rc = tma_setup(h->tma, h->buf, cfg->dtype == HEAT_F32, h->nx, h->lrows, h->pitch, g_err);
+        if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
+    }
+
+    if (cfg->nranks > 1 && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE)) {
+        const NcclApi& N = nccl_api();
+        if (!N.ok) { heat_destroy(h); return fail(HEAT_ERR_NCCL, "heat_init: NCCL not available (libnccl.so.2 could not be loaded)"); }
+        ncclUniqueId id;
+        memcpy(&id, cfg->nccl_id, sizeof id);
+        ncclResult_t r = N.CommInitRank(&h->comm, cfg->nranks, id, cfg->rank);
+        if (r != 0) {
+            int c = fail(HEAT_ERR_NCCL, "ncclCommInitRank failed: %s", N.GetErrorString(r));
+            std::string keep = g_err; h->comm = nullptr; heat_destroy(h); g_err = keep;
+            return c;
+        }
+    }
+    if (field) {
+        rc = heat_set_field(h, field, h->nx, 0);
+        if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
+    }
+    *out = h;
+    return HEAT_OK;
+#undef INIT_TRY
+}
+
+int heat_halo_exchange(heat_handle* h) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_halo_exchange: null handle");
+    if (h->cfg.nranks <= 1) return HEAT_OK;
+    CUDA_TRY(cudaSetDevice(h->dev));
+    int rc = wait_comm(h);
+    if (rc) return rc;
+    rc = exchange(h, h->cur, h->s_compute);
+    if (rc) return rc;
+    h->valid_ghost = h->g;
+    return HEAT_OK;
+}
+
+int heat_step(heat_handle* h, int nt) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_step: null handle");
+    if (nt < 0) return fail(HEAT_ERR_INVALID, "heat_step: nt must be >= 0 (got %d)", nt);
+    CUDA_TRY(cudaSetDevice(h->dev));
+    CUDA_TRY(cudaEventRecord(h->ev_t0, h->s_compute));
+    const bool multi = h->cfg.nranks > 1;
+    if (nt > 0 && h->nx >= 3 && h->ny >= 3) {
+        if (h->kernel == HEAT_KERNEL_RESIDENT) {
+            CUDA_TRY(HEAT_DISPATCH(h, launch_resident_t, h, h->buf[h->cur], h->buf[h->cur ^ 1], nt, h->s_compute));
+            h->cur ^= 1;
+        } else if (!multi) {
+            for (int t = 0; t < nt; ++t) {
+                CUDA_TRY(update_rows(h, 1, h->ny - 2, h->s_compute));
+                h->cur ^= 1;
+            }
+        } else {
+            const bool overlap = (h->cfg.flags & HEAT_FLAG_OVERLAP) && h->nrows >= 2 * h->g;
+            const int own_lo = h->row0, own_hi = h->row0 + h->nrows - 1;
+            for (int t = 0; t < nt; ++t) {
+                int rc = wait_comm(h);
+                if (rc) return rc;
+                if (h->valid_ghost == 0) {      // only after heat_set_field races or SKIP_EXCHANGE
+                    rc = exchange(h, h->cur, h->s_compute);
+                    if (rc) return rc;
+                    h->valid_ghost = h->g;
+                }
+                const int e = h->valid_ghost - 1;   // ghost rows still valid after this step
+                if (e == 0 && overlap) {
+                    // edge strips first, then their exchange on s_comm behind the interior update
+                    CUDA_TRY(update_rows(h, own_lo, own_lo + h->g - 1, h->s_compute));
+                    CUDA_TRY(update_rows(h, own_hi - h->g + 1, own_hi, h->s_compute));
+                    CUDA_TRY(cudaEventRecord(h->ev_boundary, h->s_compute));
+                    CUDA_TRY(cudaStreamWaitEvent(h->s_comm, h->ev_boundary, 0));
+                    rc = exchange(h, h->cur ^ 1, h->s_comm);
+                    if (rc) return rc;
+                    CUDA_TRY(cudaEventRecord(h->ev_comm, h->s_comm));
+                    h->comm_pending = true;
+                    CUDA_TRY(update_rows(h, own_lo + h->g, own_hi - h->g, h->s_compute));
+                    h->valid_ghost = h->g;
+                } else {
+                    CUDA_TRY(update_rows(h, own_lo - e, own_hi + e, h->s_compute));
+                    h->valid_ghost = e;
+                    if (e == 0) {
+                        rc = exchange(h, h->cur ^ 1, h->s_compute);
+                        if (rc) return rc;
+                        h->valid_ghost = h->g;
+                    }
+                }
+                h->cur ^= 1;
+            }
+            int rc = wait_comm(h);   // the timed region of this call ends after its last exchange
+            if (rc) return rc;
+        }
+        h->steps_total += (uint64_t)nt;
+    }
+    CUDA_TRY(cudaEventRecord(h->ev_t1, h->s_compute));
+    h->timed = true;
+    return HEAT_OK;
+}
+
+int heat_sync(heat_handle* h) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_sync: null handle");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    CUDA_TRY(cudaStreamSynchronize(h->s_comm));
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    return HEAT_OK;
+}
+
+int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_gather: null handle");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    int rc = wait_comm(h);
+    if (rc) return rc;
+    const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    const size_t dense = (size_t)h->nx * h->esize;
+    if (global_root < 0 || h->cfg.nranks == 1) {
+        if (!dst) return fail(HEAT_ERR_INVALID, "heat_gather: null destination");
+        CUDA_TRY(cudaMemcpy2DAsync(dst, dense, row_ptr(h, h->cur, h->g), row_bytes(h), dense, h->nrows, kind, h->s_compute));
+        CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+        return HEAT_OK;
+    }
+    if (global_root >= h->cfg.nranks) return fail(HEAT_ERR_INVALID, "heat_gather: root %d out of range", global_root);
+    if (!h->comm) return fail(HEAT_ERR_NCCL, "heat_gather: no communicator (SKIP_EXCHANGE build of the handle?)");
+    const NcclApi& N = nccl_api();
+    const int dt = h->cfg.dtype == HEAT_F32 ? ncclFloat32 : ncclFloat64;
+    if (h->cfg.rank != global_root) {
+        NCCL_TRY(N.Send(row_ptr(h, h->cur, h->g), (size_t)h->nrows * h->pitch, dt, global_root, h->comm, h->s_compute));
+        CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+        return HEAT_OK;
+    }
+    if (!dst) return fail(HEAT_ERR_INVALID, "heat_gather: root needs a destination");
+    for (int r = 0; r < h->cfg.nranks; ++r) {
+        int r0, nr;
+        heat_slab_partition(h->ny, h->cfg.nranks, r, &r0, &nr);
+        char* out = (char*)dst + (size_t)r0 * dense;
+        if (r == h->cfg.rank) {
+            CUDA_TRY(cudaMemcpy2DAsync(out, dense, row_ptr(h, h->cur, h->g), row_bytes(h), dense, nr, kind, h->s_compute));
+            continue;
+        }
+        const size_t need = (size_t)nr * row_bytes(h);
+        if (need > h->stage_bytes) {
+            CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+            cudaFree(h->d_stage);
+            h->d_stage = nullptr;
+            h->stage_bytes = 0;
+            CUDA_TRY(cudaMalloc(&h->d_stage, need));
+            h->stage_bytes = need;
+        }
+        NCCL_TRY(N.Recv(h->d_stage, (size_t)nr * h->pitch, dt, r, h->comm, h->s_compute));
+        CUDA_TRY(cudaMemcpy2DAsync(out, dense, h->d_stage, row_bytes(h), dense, nr, kind, h->s_compute));
+        CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    return HEAT_OK;
+}
+
+int heat_checksum(heat_handle* h, double* sum) {
+    if (!h || !sum) return fail(HEAT_ERR_INVALID, "heat_checksum: null argument");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    int rc = wait_comm(h);
+    if (rc) return rc;
+    if (!h->d_partials) {
+        CUDA_TRY(cudaMalloc(&h->d_partials, kSumBlocks * sizeof(double)));
+        CUDA_TRY(cudaMalloc(&h->d_sum, sizeof(double)));
+    }
+    const int yb = h->g, ye = h->g + h->nrows;
+    if (h->cfg.dtype == HEAT_F32)
+        heat_sum_partial_kernel<float><<<kSumBlocks, 256, 0, h->s_compute>>>((const float*)h->buf[h->cur], h->nx, h->pitch, yb, ye, h->d_partials);
+    else
+        heat_sum_partial_kernel<double><<<kSumBlocks, 256, 0, h->s_compute>>>((const double*)h->buf[h->cur], h->nx, h->pitch, yb, ye, h->d_partials);
+    CUDA_TRY(cudaGetLastError());
+    heat_sum_final_kernel<<<1, 32, 0, h->s_compute>>>(h->d_partials, kSumBlocks, h->d_sum);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(sum, h->d_sum, sizeof(double), cudaMemcpyDeviceToHost, h->s_compute));
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    return HEAT_OK;
+}
+
+int heat_get_info(heat_handle* h, heat_info* info) {
+    if (!h || !info) return fail(HEAT_ERR_INVALID, "heat_get_info: null argument");
+    info->nx = h->nx; info->ny = h->ny;
+    info->row0 = h->row0; info->nrows = h->nrows;
+    info->ghost = h->g;
+    info->kernel = h->kernel; info->tblock = h->tblock;
+    info->pitch = h->pitch;
+    info->buf[0] = h->buf[0]; info->buf[1] = h->buf[1];
+    info->current = h->cur;
+    info->device = h->dev;
+    return HEAT_OK;
+}
+
+int heat_get_timing(heat_handle* h, heat_timing* t) {
+    if (!h || !t) return fail(HEAT_ERR_INVALID, "heat_get_timing: null argument");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    float ms = 0.f, hms = 0.f;
+    if (h->timed) {
+        CUDA_TRY(cudaEventSynchronize(h->ev_t1));
+        CUDA_TRY(cudaEventElapsedTime(&ms, h->ev_t0, h->ev_t1));
+    }
+    if (h->halo_timed) {
+        CUDA_TRY(cudaEventSynchronize(h->ev_h1));
+        CUDA_TRY(cudaEventElapsedTime(&hms, h->ev_h0, h->ev_h1));
+    }
+    t->last_step_ms = ms;
+    t->last_halo_ms = hms;
+    t->steps_total = h->steps_total;
+    t->kernel_launches = h->launches;
+    t->halo_exchanges = h->exchanges;
+    return HEAT_OK;
+}
+
+}  // extern "C"

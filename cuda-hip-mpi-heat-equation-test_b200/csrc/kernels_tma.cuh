@@ -1,0 +1,234 @@
+// kernels_tma.cuh — TMA-fed variant of the single-step update (sm_100a).
+//
+// A CTA owns a column strip BX cells wide and a segment of rows.  One elected thread streams the
+// strip down through a ring of S shared-memory stages with cp.async.bulk.tensor.2d (SASS: UTMALDG):
+// each stage is a (BX + 2V) x BY box whose first column is x0 - V, i.e. the strip plus one 16-byte
+// vector of halo on either side, so that a lane's own vector sits 16-byte aligned in shared memory
+// and the x-1 / x+1 cells of the strip's edge lanes are already there.  Out-of-range box columns
+// and rows are zero-filled by the TMA unit and only ever feed cells that are not updated.
+// Completion is signalled on an mbarrier per stage (complete_tx::bytes); the 256 consumer threads
+// keep a rolling 3-row register window per row-subgroup, take x-neighbours by warp shuffle, and
+// store results straight from registers with 128-bit coalesced stores.  S-1 boxes (S-1 x ~17 KB)
+// are in flight per CTA, 3 CTAs per SM — enough bytes in flight to cover HBM latency without
+// depending on occupancy or register-staged loads.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <string>
+
+#include "stencil_ops.cuh"
+
+namespace heat {
+
+struct TmaState {
+    CUtensorMap map[2];
+    bool ready = false;
+    int box_w = 0, box_h = 0;
+};
+
+constexpr int kTmaBX = 128;      // strip width in cells
+constexpr int kTmaBY = 16;       // rows per stage
+constexpr int kTmaStages = 4;
+constexpr int kTmaThreads = 256;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) {
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int cx, int cy, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(cx), "r"(cy), "r"(smem_u32(bar)) : "memory");
+}
+
+template <typename T, int ORDER, bool FMA>
+__global__ void __launch_bounds__(kTmaThreads)
+heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
+                int y_begin, int y_end, int seg_rows, T rx, T ry) {
+    constexpr int V = Pack<T>::V;
+    using P = Pack<T>;
+    constexpr int BX = kTmaBX, BY = kTmaBY, S = kTmaStages;
+    constexpr int BW = BX + 2 * V;                 // box width (cells)
+    constexpr int LPR = BX / V;                    // lanes per row
+    constexpr int NSUB = kTmaThreads / LPR;        // row subgroups
+    constexpr int RPS = BY / NSUB;                 // rows per subgroup per stage
+    constexpr int RING = S * BY;                   // ring depth in rows
+    static_assert(BY % NSUB == 0 && LPR % 32 == 0, "tile shape");
+    constexpr unsigned kStageBytes = BY * BW * sizeof(T);
+    static_assert(kStageBytes % 128 == 0, "stage must keep 128-byte alignment");
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    T* ring = reinterpret_cast<T*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)S * kStageBytes);
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int col = tid % LPR, sub = tid / LPR;
+    const int x0 = blockIdx.x * BX;
+    const int ys = y_begin + blockIdx.y * seg_rows;
+    const int ye = min(ys + seg_rows, y_end);
+    if (ys >= ye) return;
+    const int np = ye - ys;                         // centres p = 1..np  (global row ys-1+p)
+    const int nstages = (np + 2 + BY - 1) / BY;     // input rows p = 0..np+1
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    auto issue = [&](int j) {
+        const int slot = j % S;
+        mbar_expect_tx(&full[slot], kStageBytes);
+        tma_load_2d(ring + (size_t)slot * BY * BW, &tmap, x0 - V, ys - 1 + j * BY, &full[slot]);
+    };
+    if (tid == 0) {
+        for (int j = 0; j < S - 1 && j < nstages; ++j) issue(j);
+    }
+
+    const long xg = (long)x0 + (long)col * V;       // this lane's first global column
+    const bool active = xg < pitch;
+    const int sx = (col + 1) * V;                   // its column inside the box
+    // lanes at a warp's edge read the adjacent cell from shared memory instead of shuffling
+    const int sxe = (lane == 0) ? sx - 1 : sx + V;
+
+    for (int j = 0; j < nstages; ++j) {
+        mbar_wait(&full[j % S], (unsigned)((j / S) & 1));
+        const int p0 = j * BY - 1 + sub * RPS;      // first centre row of this subgroup
+        P win[RPS + 2];
+        T edg[RPS];
+#pragma unroll
+        for (int i = 0; i < RPS + 2; ++i) {
+            const int p = p0 - 1 + i;
+            if (p >= 0) win[i] = *reinterpret_cast<const P*>(ring + (size_t)(p % RING) * BW + sx);
+            else {
+#pragma unroll
+                for (int v = 0; v < V; ++v) win[i].v[v] = T(0);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < RPS; ++i) {
+            const int p = p0 + i;
+            edg[i] = (p >= 0 && (lane == 0 || lane == 31)) ? ring[(size_t)(p % RING) * BW + sxe] : T(0);
+        }
+#pragma unroll
+        for (int i = 0; i < RPS; ++i) {
+            const int p = p0 + i;
+            const P& s = win[i];
+            const P& c = win[i + 1];
+            const P& n = win[i + 2];
+            T left = __shfl_up_sync(0xffffffffu, c.v[V - 1], 1);
+            T right = __shfl_down_sync(0xffffffffu, c.v[0], 1);
+            if (lane == 0) left = edg[i];
+            if (lane == 31) right = edg[i];
+            P o;
+#pragma unroll
+            for (int v = 0; v < V; ++v) {
+                const T w = (v == 0) ? left : c.v[v - 1];
+                const T e = (v == V - 1) ? right : c.v[v + 1];
+                const T r = stencil<T, ORDER, FMA>(c.v[v], w, e, s.v[v], n.v[v], rx, ry);
+                const long x = xg + v;
+                o.v[v] = (x >= 1 && x <= nx - 2) ? r : c.v[v];
+            }
+            if (active && p >= 1 && p <= np)
+                *reinterpret_cast<P*>(dst + (long)(ys - 1 + p) * pitch + xg) = o;
+        }
+        __syncthreads();                            // everyone is done with stage j-1 (and j's reads)
+        if (tid == 0 && j + S - 1 < nstages) issue(j + S - 1);
+    }
+}
+
+// ------------------------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+
+inline PFN_encodeTiled get_encode_tiled() {
+    static PFN_encodeTiled fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (PFN_encodeTiled)p;
+    }();
+    return fn;
+}
+
+// one 2-D map per ping-pong buffer: dims {pitch, rows}, box {box_w, box_h}, zero fill out of range
+inline int tma_make_map(CUtensorMap* map, void* base, bool f32, long pitch, int rows, int box_w, int box_h,
+                        std::string& err) {
+    PFN_encodeTiled enc = get_encode_tiled();
+    if (!enc) { err = "cuTensorMapEncodeTiled is not available from this driver"; return -5; }
+    const size_t es = f32 ? 4 : 8;
+    cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch * es};
+    cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)box_h};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims,
+                     strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        err = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r);
+        return -2;
+    }
+    return 0;
+}
+
+inline int tma_setup(TmaState& st, void* const buf[2], bool f32, int nx, int rows, long pitch, std::string& err) {
+    (void)nx;
+    const int V = f32 ? 4 : 2;
+    st.box_w = kTmaBX + 2 * V;
+    st.box_h = kTmaBY;
+    for (int b = 0; b < 2; ++b) {
+        int rc = tma_make_map(&st.map[b], buf[b], f32, pitch, rows, st.box_w, st.box_h, err);
+        if (rc) return rc;
+    }
+    st.ready = true;
+    return 0;
+}
+
+template <typename T, int ORDER, bool FMA>
+inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx, long pitch, int yb, int ye,
+                                   T rx, T ry, int sm_count, cudaStream_t s) {
+    constexpr int V = Pack<T>::V;
+    constexpr size_t smem = (size_t)kTmaStages * kTmaBY * (kTmaBX + 2 * V) * sizeof(T) + kTmaStages * sizeof(uint64_t);
+    auto k = heat_tma_kernel<T, ORDER, FMA>;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int rows = ye - yb;
+    const int gx = (int)((pitch + kTmaBX - 1) / kTmaBX);
+    int seg = 0;
+    if (const char* v = getenv("HEAT_TMA_SEG")) seg = atoi(v);
+    if (seg <= 0) {
+        const int target = sm_count * 12;
+        const int nseg = std::max(1, target / gx);
+        seg = (rows + nseg - 1) / nseg;
+        seg = std::max(64, (seg + kTmaBY - 1) / kTmaBY * kTmaBY);
+    }
+    seg = std::min(seg, rows);
+    const int gy = (rows + seg - 1) / seg;
+    k<<<dim3(gx, gy), kTmaThreads, smem, s>>>(st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry);
+    return cudaGetLastError();
+}
+
+}  // namespace heat

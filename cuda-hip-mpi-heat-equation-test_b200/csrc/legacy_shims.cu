@@ -1,0 +1,71 @@
+// legacy_shims.cu — the reference's only C ABI, re-implemented for sm_100a with identical
+// signatures and conventions, so that fortran/hip/heat.F90 (bind(c) interfaces at :48-102) links
+// against libheat.so unchanged: ghosted i-contiguous arrays, caller-owned device buffers,
+// asynchronous on the default stream, no return value, caller synchronises.
+// ref: fortran/hip/heat_kernel.cpp:26 (idx), :29 (idx_s), :31-61, :63-150.
+#include "../../include/heat_b200.h"
+#include "stencil_ops.cuh"
+
+namespace {
+
+// element (i, j), 1-based interior, of a ghosted array: (i-1+ng) + (nx+2ng)*(j-1+ng)
+__device__ __forceinline__ long gidx(int i, int j, int nx, int ng) {
+    return (long)(i - 1 + ng) + (long)(nx + 2 * ng) * (j - 1 + ng);
+}
+
+__global__ void __launch_bounds__(256)
+legacy_heat_eqn_kernel(double* __restrict__ Td, const double* __restrict__ Td_old, double r, int nx, int ny, int ng) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+    if (i > nx || j > ny) return;
+    const long w = nx + 2 * ng;
+    const double* p = Td_old + gidx(i, j, nx, ng);
+    Td[gidx(i, j, nx, ng)] =
+        heat::stencil<double, heat::ORDER_FORTRAN, false>(p[0], p[-1], p[1], p[-w], p[w], r, r);
+}
+
+// which: 0 = pack both edge lines, 1 = unpack into the low ghost, 2 = unpack into the high ghost
+__global__ void __launch_bounds__(256)
+legacy_swap_kernel(double* __restrict__ Td, double* __restrict__ a, double* __restrict__ b, int nx, int ny, int ng, int which) {
+    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long)ng * ny) return;
+    const int i = (int)(t % ng) + 1, j = (int)(t / ng) + 1;
+    const long s = (long)(i - 1) + (long)ng * (j - 1);                  // idx_s
+    if (which == 0) {
+        a[s] = Td[gidx(i, j, nx, ng)];
+        b[s] = Td[gidx(nx - ng + i, j, nx, ng)];
+    } else if (which == 1) {
+        Td[gidx(i - ng, j, nx, ng)] = a[s];
+    } else {
+        Td[gidx(nx + i, j, nx, ng)] = a[s];
+    }
+}
+
+inline unsigned blocks_for(long n) { return (unsigned)((n + 255) / 256); }
+
+}  // namespace
+
+extern "C" {
+
+void launch_heat_eqn(double* Td, double* Td_old, double r, int nx, int ny, int ng) {
+    if (nx < 1 || ny < 1 || ng < 1) return;
+    dim3 block(128, 2), grid((nx + 127) / 128, (ny + 1) / 2);
+    legacy_heat_eqn_kernel<<<grid, block>>>(Td, Td_old, r, nx, ny, ng);
+}
+
+void launch_send(double* Td, double* Tds1, double* Tds2, int nx, int ny, int ng) {
+    if (nx < 1 || ny < 1 || ng < 1) return;
+    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tds1, Tds2, nx, ny, ng, 0);
+}
+
+void launch_recv1(double* Td, double* Tdr, int nx, int ny, int ng) {
+    if (nx < 1 || ny < 1 || ng < 1) return;
+    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tdr, nullptr, nx, ny, ng, 1);
+}
+
+void launch_recv2(double* Td, double* Tdr, int nx, int ny, int ng) {
+    if (nx < 1 || ny < 1 || ng < 1) return;
+    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tdr, nullptr, nx, ny, ng, 2);
+}
+
+}  // extern "C"

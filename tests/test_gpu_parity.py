@@ -1,0 +1,291 @@
+"""GPU parity tests: every call goes through the C ABI of libheat.so (via heatb200's ctypes layer) and is
+compared with the oracle / the golden fixtures.  Bar: bit-exact for the default (no-FMA) mode in fp64 and
+fp32; <= 1e-12 (fp64) / <= 1e-5 (fp32 vs the fp64 oracle) relative otherwise — BASELINE.json north_star."""
+import numpy as np
+import pytest
+
+import heatb200
+from heatb200 import _lib, config, ic
+from oracle import c_oracle, heat_oracle as ho
+
+pytestmark = pytest.mark.gpu
+
+KERNELS = ["simple", "stream", "tma"]
+ORDERS = ["fortran", "pycuda", "pyserial"]
+R100 = 0.24999999999999997          # r for n = 100 (fortran/mpi+cuda/input.dat): not a power of two
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint64 if a.dtype == np.float64 else np.uint32)
+
+
+def assert_bit_equal(a, b):
+    assert a.shape == b.shape and a.dtype == b.dtype
+    if not np.array_equal(bits(a), bits(b)):
+        bad = np.argwhere(bits(a) != bits(b))
+        raise AssertionError("%d cells differ, first at %s, max abs diff %g" % (len(bad), bad[0], np.abs(a - b).max()))
+
+
+def rand_field(shape, dtype=np.float64, seed=0):
+    return (1.0 + np.random.default_rng(seed).random(shape)).astype(dtype)
+
+
+# ------------------------------------------------------------------ golden fixtures (reference outputs)
+def test_pyserial_dropin_matches_reference_run(golden):
+    from heatb200 import serial
+    serial.configure(n=31)
+    serial.diffuse(10)
+    assert_bit_equal(serial.u, golden("pyserial_31.npz")["u"])
+    assert float(serial.u.sum()) == 1041.943124294281
+
+
+@pytest.mark.parametrize("kernel", KERNELS + ["resident", "auto"])
+def test_pyserial_case_every_kernel(golden, kernel):
+    u0 = ic.hat_pyserial(31, 31)
+    _, _, _, cx, cy = config.derive_python(31, 31)
+    got = heatb200.march(u0, 11, cx, cy, order="pyserial", kernel=kernel)
+    assert_bit_equal(got, golden("pyserial_31.npz")["u"])
+
+
+@pytest.mark.parametrize("kernel", KERNELS + ["resident"])
+def test_hip_kernel_goldens(golden, kernel):
+    g = golden("hip_slabs_n100.npz")
+    r = float(g["r"])
+    # the ghosted 102 x 102 array is a 102 x 102 field whose ring is the ghost layer
+    got = heatb200.march(ho.ic_mpi_ghosted(100, 100), 10, r, order="fortran", kernel=kernel)
+    assert_bit_equal(got, g["P1_rank0"])
+    got = heatb200.march(g["rand_u0"], 5, r, order="fortran", kernel=kernel)
+    assert_bit_equal(got, g["rand_u5"])
+
+
+@pytest.mark.parametrize("kernel", KERNELS + ["resident"])
+@pytest.mark.parametrize("tag", ["r025", "rn100"])
+def test_pycuda_kernel_goldens(golden, kernel, tag):
+    g = golden("pycuda_kernel.npz")
+    got = heatb200.march(g["u0"], 5, float(g["r_" + tag]), order="pycuda", kernel=kernel)
+    assert_bit_equal(got, g["u5_" + tag])
+
+
+# ------------------------------------------------------------------ oracle, seeded inputs, ragged shapes
+SHAPES = [(3, 3), (4, 5), (5, 17), (31, 31), (100, 100), (130, 257), (77, 1000), (515, 64)]
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("order", ORDERS)
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_kernels_bit_exact_vs_oracle(kernel, order, dtype):
+    for shape in SHAPES:
+        u0 = rand_field(shape, dtype, seed=shape[0])
+        rx, ry = dtype(R100), dtype(0.2437)
+        want = ho.march(u0, 7, ho.ORDERS[order], rx, ry)
+        got = heatb200.march(u0, 7, float(rx), float(ry), order=order, kernel=kernel)
+        assert_bit_equal(got, want)
+
+
+@pytest.mark.parametrize("order", ORDERS)
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_resident_kernel_bit_exact(order, dtype):
+    for shape in [(3, 3), (31, 31), (100, 100), (64, 190)]:
+        u0 = rand_field(shape, dtype, seed=3)
+        want = ho.march(u0, 40, ho.ORDERS[order], dtype(R100), dtype(0.2437))
+        got = heatb200.march(u0, 40, float(dtype(R100)), float(dtype(0.2437)), order=order, kernel="resident")
+        assert_bit_equal(got, want)
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (1, 40), (2, 9), (9, 2), (40, 1)])
+def test_degenerate_fields_are_untouched(shape):
+    u0 = rand_field(shape)
+    for kernel in ["auto", "simple"]:
+        assert_bit_equal(heatb200.march(u0, 3, 0.25, kernel=kernel), u0)
+
+
+def test_zero_steps_and_repeated_steps():
+    u0 = rand_field((65, 130))
+    with heatb200.HeatSolver(u0, R100, kernel="stream") as s:
+        s.step(0)
+        assert_bit_equal(s.gather(), u0)
+        for _ in range(5):
+            s.step(1)
+        a = s.gather()
+        t = s.timing()
+        assert t.steps_total == 5 and t.kernel_launches == 5
+    assert_bit_equal(a, ho.march(u0, 5, 0, R100))
+
+
+def test_boundary_ring_is_preserved_exactly():
+    u0 = rand_field((90, 140), seed=5)
+    u0[0, :] = 3.25
+    u0[:, -1] = -7.5
+    for kernel in KERNELS:
+        got = heatb200.march(u0, 9, R100, kernel=kernel)
+        for sl in [(0, slice(None)), (-1, slice(None)), (slice(None), 0), (slice(None), -1)]:
+            assert_bit_equal(got[sl], u0[sl])
+
+
+# ------------------------------------------------------------------ tolerance modes
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("order", ORDERS)
+def test_fmad_mode_within_1e12(kernel, order):
+    u0 = rand_field((200, 333), seed=9)
+    want = ho.march(u0, 50, ho.ORDERS[order], R100, 0.2437)
+    got = heatb200.march(u0, 50, R100, 0.2437, order=order, kernel=kernel, fmad=True)
+    assert np.max(np.abs(got - want) / np.abs(want)) <= 1e-12
+
+
+@pytest.mark.parametrize("fmad", [False, True])
+def test_fp32_within_1e5_of_fp64_oracle(fmad):
+    u0 = rand_field((200, 333), seed=11)
+    want = ho.march(u0, 50, 0, R100)
+    got = heatb200.march(u0.astype(np.float32), 50, R100, kernel="stream", fmad=fmad)
+    assert got.dtype == np.float32
+    assert np.max(np.abs(got - want) / np.abs(want)) <= 1e-5
+
+
+# ------------------------------------------------------------------ input.dat driven, shipped decks
+@pytest.mark.parametrize("deck_text,y_hi", [
+    ("100 0.25 0.05 2.0 1000", 1.0),        # fortran/cuda_cuf/input.dat, fortran/cuda_kernel/input.dat
+    ("1024 0.25 0.05 2.0 30", 1.5),         # fortran/serial/input.dat
+])
+def test_shipped_input_decks(deck_text, y_hi):
+    deck = config.parse_input_dat(deck_text)
+    delta, _, r = deck.derive()
+    assert (delta, r) == (ho.derive_fortran(deck.n, deck.sigma, deck.nu, deck.dom_len)[0],
+                          ho.derive_fortran(deck.n, deck.sigma, deck.nu, deck.dom_len)[2])
+    u0 = ic.hat_fortran(deck.n, deck.dom_len, delta, y_hi)
+    assert_bit_equal(u0, ho.ic_fortran(deck.n, deck.dom_len, y_hi))
+    want = c_oracle.march(u0, deck.ntime, 0, r)
+    for kernel in ["auto", "stream", "tma"]:
+        assert_bit_equal(heatb200.march(u0, deck.ntime, r, kernel=kernel), want)
+
+
+def test_cuda_dropin_small():
+    from heatb200 import cuda
+    cuda.configure(n=256, nt_=19, hat=True)
+    u0 = cuda.u_new.copy()
+    out = cuda.run()
+    assert out.shape == (256, 256)
+    assert_bit_equal(out, ho.march(u0, 20, ho.ORDER_PYCUDA, cuda.r))
+    # the call-compatible single launch
+    cuda.configure(n=64, nt_=0, hat=True)
+    new, old = cuda.u_new.copy(), cuda.u_new.copy()
+    cuda.heatCalculate(cuda.drv.InOut(new.ravel()), cuda.drv.In(old.ravel()), block=(32, 8, 1), grid=(2, 8))
+    assert_bit_equal(new, ho.march(old, 1, ho.ORDER_PYCUDA, cuda.r))
+    # as shipped (empty hat slice) the field is the fixed point 1
+    cuda.configure(n=128, nt_=3)
+    assert (cuda.run() == 1.0).all()
+
+
+# ------------------------------------------------------------------ full-size properties (BASELINE sizes)
+def test_4096_kernels_agree_and_match_c_oracle():
+    n = 4096
+    deck = config.InputDeck(n, 0.25, 0.05, 2.0, 8)
+    delta, _, r = deck.derive()
+    assert r == 0.25
+    u0 = ic.hat_fortran(n, 2.0, delta)
+    want = c_oracle.march(u0, 8, 0, r, omp=True)
+    outs = {k: heatb200.march(u0, 8, r, kernel=k) for k in KERNELS}
+    for k in KERNELS:
+        assert_bit_equal(outs[k], want)
+    a = outs["tma"]
+    assert np.array_equal(a, a.T)                      # transpose symmetry (SURVEY §4 iii)
+    assert a.min() >= 1.0 and a.max() <= 2.0           # maximum principle (SURVEY §4 iv)
+    # exact-arithmetic window: every op order gives the same bits (SURVEY §4 ii)
+    for order in ["pycuda", "pyserial"]:
+        assert_bit_equal(heatb200.march(u0, 8, r, order=order, kernel="stream"), a)
+
+
+def test_16384_random_field_kernels_agree_and_linear():
+    """At the north-star size the oracle is too slow; use kernel-vs-kernel bit equality (independent code
+    paths) plus linearity of the update: march(a*u + b) == a*march(u) + b for power-of-two a (exact in fp)."""
+    import torch
+    n = 16384
+    g = torch.Generator(device="cuda").manual_seed(0)
+    u = 1.0 + torch.rand((n, n), dtype=torch.float64, device="cuda", generator=g)
+    res = {}
+    for k in ["stream", "tma"]:
+        with heatb200.HeatSolver(None, 0.25, nx=n, ny=n, dtype=np.float64, kernel=k) as s:
+            s.set_field_from_tensor(u)
+            s.step(6)
+            out = torch.empty_like(u)
+            s.gather_into_tensor(out)
+            res[k] = out
+            ck = s.checksum()
+            assert abs(ck - float(out.sum())) <= 1e-9 * abs(ck)
+    assert torch.equal(res["stream"], res["tma"])
+    with heatb200.HeatSolver(None, 0.25, nx=n, ny=n, dtype=np.float64, kernel="tma") as s:
+        s.set_field_from_tensor(4.0 * u + 8.0)
+        s.step(6)
+        out = torch.empty_like(u)
+        s.gather_into_tensor(out)
+    assert torch.equal(out, 4.0 * res["tma"] + 8.0)
+    # spot-check a 64-row band against the C oracle (bands are independent for 6 steps if cut 6 rows deep)
+    band = u[1000:1000 + 64 + 12].cpu().numpy()
+    want = c_oracle.march(band, 6, 0, 0.25, omp=True)[6:-6]
+    assert_bit_equal(res["tma"][1006:1006 + 64].cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------ torch buffers, checksum, errors
+def test_external_torch_buffers_and_unaligned_pitch():
+    import torch
+    u0 = rand_field((50, 101), seed=2)
+    b0 = torch.zeros((50, 101), dtype=torch.float64, device="cuda")
+    b1 = torch.zeros_like(b0)
+    with heatb200.HeatSolver(u0, R100, buffers=(b0, b1)) as s:
+        assert s.kernel_name == "simple"            # pitch 101 is not 16-byte friendly
+        s.step(4)
+        got = s.gather()
+        cur = (b0, b1)[s.info().current]
+    assert_bit_equal(got, ho.march(u0, 4, 0, R100))
+    assert_bit_equal(cur.cpu().numpy(), got)       # the caller's tensors ARE the storage
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.HeatSolver(u0, R100, buffers=(b0, b1), kernel="stream")
+    assert e.value.code == _lib.ERR_UNSUPPORTED
+
+
+def test_checksum_deterministic_and_close():
+    u0 = rand_field((300, 500), seed=4)
+    with heatb200.HeatSolver(u0, R100) as s:
+        s.step(3)
+        a, b = s.checksum(), s.checksum()
+        assert a == b
+        assert abs(a - s.gather().sum()) <= 1e-10 * abs(a)
+
+
+def test_error_paths():
+    u0 = rand_field((16, 16))
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.HeatSolver(u0, 0.25, device=99)
+    assert e.value.code == _lib.ERR_INVALID and "device" in str(e.value)
+    with pytest.raises(heatb200.HeatError):
+        heatb200.HeatSolver(u0, 0.25, nranks=2, rank=0, ny=32)             # no nccl id
+    with pytest.raises(heatb200.HeatError):
+        heatb200.HeatSolver(rand_field((400, 400)), 0.25, kernel="resident")  # does not fit one CTA
+    with heatb200.HeatSolver(u0, 0.25) as s:
+        with pytest.raises(heatb200.HeatError):
+            s.step(-1)
+
+
+def test_legacy_hip_abi(golden):
+    """launch_heat_eqn / launch_send / launch_recv1 / launch_recv2 with the reference's signatures on
+    caller-owned ghosted device arrays, driven like fortran/hip/heat.F90:234-252,198-228 for P = 2."""
+    import ctypes as C
+    import torch
+    g = golden("hip_slabs_n100.npz")
+    L, r, nxl, ny, ng = heatb200.lib(), float(g["r"]), 50, 100, 1
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    p = lambda t: C.c_void_p(t.data_ptr())
+    Td = [dev(ho.ic_mpi_ghosted(nxl, ny, q == 0, q == 1)) for q in range(2)]
+    s1 = [torch.zeros(ng * ny, dtype=torch.float64, device="cuda") for _ in range(2)]
+    s2 = [torch.zeros(ng * ny, dtype=torch.float64, device="cuda") for _ in range(2)]
+    for _ in range(10):
+        for q in range(2):
+            old = Td[q].clone()                                    # hipMemcpy D2D, heat.F90:243
+            L.launch_heat_eqn(p(Td[q]), p(old), r, nxl, ny, ng)
+            torch.cuda.synchronize()
+            L.launch_send(p(Td[q]), p(s1[q]), p(s2[q]), nxl, ny, ng)
+        torch.cuda.synchronize()
+        L.launch_recv1(p(Td[1]), p(s2[0]), nxl, ny, ng)            # rank 1's left ghost <- rank 0's last line
+        L.launch_recv2(p(Td[0]), p(s1[1]), nxl, ny, ng)            # rank 0's right ghost <- rank 1's first line
+        torch.cuda.synchronize()
+    for q in range(2):
+        assert_bit_equal(Td[q].cpu().numpy(), g["P2_rank%d" % q])

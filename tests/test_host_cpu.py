@@ -1,0 +1,127 @@
+"""CPU: the C-ABI library loads and exports every symbol include/heat_b200.h declares, the pure-host entry
+points work without a GPU, compute entry points fail loudly (no CPU fallback), and the host layer
+(input.dat parsing, parameter derivation, initial conditions, drop-in module globals) matches the oracle."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import heatb200
+from heatb200 import _lib, config, ic
+from oracle import heat_oracle as ho
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "heat_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b((?:heat|launch)_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    L = heatb200.lib()
+    names = declared_symbols()
+    assert len(names) >= 19
+    for n in names:
+        assert hasattr(L, n), "libheat.so does not export %s" % n
+    assert sorted(_lib.PROTOTYPES) == names, "ctypes prototypes and header disagree"
+
+
+def test_config_struct_matches_header_layout():
+    # struct_size is checked by heat_init; a mismatch is reported as HEAT_ERR_INVALID, never UB
+    cfg = _lib.HeatConfig()
+    cfg.struct_size = 4
+    h = C.c_void_p()
+    rc = heatb200.lib().heat_init(C.byref(h), C.byref(cfg), None)
+    assert rc == _lib.ERR_INVALID and b"struct_size" in heatb200.lib().heat_last_error()
+    assert C.sizeof(_lib.HeatConfig) == 104
+
+
+def test_slab_partition():
+    for ny, P in [(100, 1), (100, 3), (32768, 8), (7, 7), (10, 4)]:
+        rows = [heatb200.slab_partition(ny, P, r) for r in range(P)]
+        assert rows[0][0] == 0 and sum(n for _, n in rows) == ny
+        for (a, n), (b, _) in zip(rows, rows[1:]):
+            assert a + n == b
+        assert max(n for _, n in rows) - min(n for _, n in rows) <= 1
+    with pytest.raises(heatb200.HeatError):
+        heatb200.slab_partition(10, 4, 4)
+
+
+def test_derive_matches_oracle_bit_for_bit():
+    for n in (31, 100, 1024, 4096, 16384, 32768, 131072, 77):
+        for L in (1.0, 2.0, 3.7):
+            d = config.InputDeck(n, 0.25, 0.05, L, 1).derive()
+            assert d == ho.derive_fortran(n, 0.25, 0.05, L)
+    assert config.derive_python(31, 31) == ho.derive_python(31, 31)
+    assert config.derive_python(4096, 4096) == ho.derive_python(4096, 4096)
+
+
+@pytest.mark.parametrize("text", [
+    "1024 0.25 0.05 2.0 30\n", "100 0.25 0.05 2.0 10 1\n", "32768 0.25 0.05 1.0 25000 0",
+    "100, 2.5d-1 ,5.0D-2\n 2.0\n1000 /", " 31 .25 .05 2. 11 / trailing junk 5 6"])
+def test_parse_input_dat_matches_oracle(text):
+    d = config.parse_input_dat(text)
+    assert (d.n, d.sigma, d.nu, d.dom_len, d.ntime, d.soln) == ho.parse_input_dat(text)
+
+
+def test_parse_input_dat_from_file_and_errors(tmp_path):
+    p = tmp_path / "input.dat"
+    p.write_text("100 0.25 0.05 2.0 1000\n")
+    assert config.parse_input_dat(str(p)).ntime == 1000
+    for bad in ["100 0.25 0.05", "", "1 0.25 0.05 2.0 10", "10.5 0.25 0.05 2.0 10", "10 0.25 0.05 2.0 -1"]:
+        with pytest.raises(ValueError):
+            config.parse_input_dat(bad + "\n")
+
+
+def test_initial_conditions_match_oracle():
+    for n in (31, 100, 257):
+        delta = ho.derive_fortran(n, 0.25, 0.05, 2.0)[0]
+        assert np.array_equal(ic.hat_fortran(n, 2.0, delta), ho.ic_fortran(n, 2.0))
+        assert np.array_equal(ic.hat_fortran(n, 2.0, delta, 1.0), ho.ic_fortran(n, 2.0, 1.0))
+        assert np.array_equal(ic.hat_pyserial(n, n), ho.ic_pyserial(n, n))
+        assert np.array_equal(ic.hat_pycuda(n, n), ho.ic_pycuda(n, n))
+        full = ic.hat_fortran(n, 2.0, delta)
+        for P in (2, 3):
+            parts = [ic.hat_fortran(n, 2.0, delta, rows=heatb200.slab_partition(n, P, r)) for r in range(P)]
+            assert np.array_equal(np.concatenate(parts), full)
+    g = ho.ic_mpi_ghosted(10, 12)
+    assert np.array_equal(ic.mpi_uniform(12, 14), g)
+    assert np.array_equal(np.concatenate([ic.mpi_uniform(12, 14, rows=(0, 5)), ic.mpi_uniform(12, 14, rows=(5, 9))]), g)
+
+
+def test_dropin_module_globals_mirror_reference(golden):
+    from heatb200 import serial, cuda
+    serial.configure(n=31)
+    g = golden("pyserial_31.npz")
+    assert (serial.nx, serial.ny, serial.nt) == (31, 31, 17)
+    assert serial.dx == float(g["dx"]) and serial.dt == float(g["dt"]) and serial.nu == .05 and serial.sigma == .25
+    assert np.array_equal(serial.u, ho.ic_pyserial(31, 31)) and (serial.un == 1).all()
+    assert np.array_equal(serial.x, np.linspace(0, 2, 31))
+    assert (cuda.nx, cuda.ny, cuda.nt) == (4096, 4096, 10000) and cuda.r == 0.25
+    assert callable(cuda.heatCalculate) and callable(serial.diffuse)
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.march(np.ones((8, 8)), 1, 0.25)
+    assert e.value.code == _lib.ERR_CUDA
+    from heatb200 import serial
+    serial.configure(n=31)
+    with pytest.raises(heatb200.HeatError):
+        serial.diffuse(10)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "cuda-hip-mpi-heat-equation-test_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b|liboracle|oracle/", src, re.M), f
