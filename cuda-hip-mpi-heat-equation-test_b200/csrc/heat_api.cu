@@ -15,6 +15,7 @@
 
 #include "kernels_basic.cuh"
 #include "kernels_tma.cuh"
+#include "kernels_temporal.cuh"
 #include "nccl_dyn.h"
 
 using namespace heat;
@@ -77,6 +78,7 @@ struct heat_handle {
     void* d_stage = nullptr;       // global-gather staging on the root (lazily allocated)
     size_t stage_bytes = 0;
     TmaState tma;                  // tensor maps for the TMA kernels (kernels_tma.cuh)
+    TemporalState temporal;        // tensor maps for the fused K-step kernel (kernels_temporal.cuh)
     int sm_count = 148;
     int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
     uint64_t steps_total = 0, launches = 0, exchanges = 0;
@@ -140,6 +142,20 @@ static cudaError_t launch_resident_t(heat_handle* h, const void* src, void* dst,
     return cudaGetLastError();
 }
 
+template <typename T, int ORDER, bool FMA>
+static cudaError_t launch_fused_t(heat_handle* h, const void* src, void* dst, int yb, int ye, cudaStream_t s) {
+    if (yb >= ye || h->nx < 3) return cudaSuccess;
+    const T rx = (T)h->cfg.rx, ry = (T)h->cfg.ry;
+    const int which = src == h->buf[0] ? 0 : 1;
+    const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;   // local rows of global rows 0, ny-1
+    h->launches++;
+    switch (h->tblock) {
+        case 2: return launch_temporal_rows<T, ORDER, FMA, 2>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s);
+        case 4: return launch_temporal_rows<T, ORDER, FMA, 4>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s);
+    }
+    return cudaErrorInvalidValue;
+}
+
 #define HEAT_DISPATCH(h, FN, ...)                                                                   \
     [&]() -> cudaError_t {                                                                          \
         const int key_ = ((h)->cfg.dtype == HEAT_F32 ? 6 : 0) + (h)->cfg.op_order * 2 + ((h)->fma ? 1 : 0); \
@@ -169,6 +185,17 @@ static cudaError_t update_rows(heat_handle* h, int glo, int ghi, cudaStream_t s)
     void* dst = h->buf[h->cur ^ 1];
     const int yb = lrow(h, glo), ye = lrow(h, ghi) + 1;
     return HEAT_DISPATCH(h, launch_rows_t, h, src, dst, yb, ye, s);
+}
+
+// K fused steps on global rows [glo, ghi] (inclusive): buf[cur] -> buf[cur^1] holds time level +K there
+static cudaError_t update_rows_fused(heat_handle* h, int glo, int ghi, cudaStream_t s) {
+    glo = std::max(glo, 1);
+    ghi = std::min(ghi, h->ny - 2);
+    if (glo > ghi) return cudaSuccess;
+    const void* src = h->buf[h->cur];
+    void* dst = h->buf[h->cur ^ 1];
+    const int yb = lrow(h, glo), ye = lrow(h, ghi) + 1;
+    return HEAT_DISPATCH(h, launch_fused_t, h, src, dst, yb, ye, s);
 }
 
 // ------------------------------------------------------------------------------------ halo exchange
@@ -218,7 +245,7 @@ static int resolve_kernel(heat_handle* h) {
     int k = c.kernel;
     if (k == HEAT_KERNEL_AUTO) {
         if (fits_resident) k = HEAT_KERNEL_RESIDENT;
-        else if (aligned) k = HEAT_KERNEL_STREAM;
+        else if (aligned) k = HEAT_KERNEL_TMA;      // measured fastest at 4096^2 and 16384^2 (profiles/)
         else k = HEAT_KERNEL_SIMPLE;
     }
     if (k == HEAT_KERNEL_RESIDENT && !fits_resident)
@@ -413,6 +440,16 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
     }
 
+    if (h->tblock > 1) {
+        if (h->tblock != 2 && h->tblock != 4) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: tblock must be 1, 2 or 4"); }
+        if (h->kernel == HEAT_KERNEL_SIMPLE || h->kernel == HEAT_KERNEL_RESIDENT) {
+            h->tblock = 1;             // unaligned caller buffers / tiny fields: fall back to single steps
+        } else {
+            rc = temporal_setup(h->temporal, h->buf, cfg->dtype == HEAT_F32, h->lrows, h->pitch, h->tblock, g_err);
+            if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
+        }
+    }
+
     if (cfg->nranks > 1 && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE)) {
         const NcclApi& N = nccl_api();
         if (!N.ok) { heat_destroy(h); return fail(HEAT_ERR_NCCL, "heat_init: NCCL not available (libnccl.so.2 could not be loaded)"); }
@@ -457,36 +494,44 @@ int heat_step(heat_handle* h, int nt) {
             CUDA_TRY(HEAT_DISPATCH(h, launch_resident_t, h, h->buf[h->cur], h->buf[h->cur ^ 1], nt, h->s_compute));
             h->cur ^= 1;
         } else if (!multi) {
-            for (int t = 0; t < nt; ++t) {
+            int t = 0;
+            for (; h->tblock > 1 && t + h->tblock <= nt; t += h->tblock) {
+                CUDA_TRY(update_rows_fused(h, 1, h->ny - 2, h->s_compute));
+                h->cur ^= 1;
+            }
+            for (; t < nt; ++t) {
                 CUDA_TRY(update_rows(h, 1, h->ny - 2, h->s_compute));
                 h->cur ^= 1;
             }
         } else {
             const bool overlap = (h->cfg.flags & HEAT_FLAG_OVERLAP) && h->nrows >= 2 * h->g;
             const int own_lo = h->row0, own_hi = h->row0 + h->nrows - 1;
-            for (int t = 0; t < nt; ++t) {
+            for (int t = 0; t < nt;) {
                 int rc = wait_comm(h);
                 if (rc) return rc;
-                if (h->valid_ghost == 0) {      // only after heat_set_field races or SKIP_EXCHANGE
+                if (h->valid_ghost == 0) {      // only after SKIP_EXCHANGE or an external reset
                     rc = exchange(h, h->cur, h->s_compute);
                     if (rc) return rc;
                     h->valid_ghost = h->g;
                 }
-                const int e = h->valid_ghost - 1;   // ghost rows still valid after this step
+                // advance K fused steps while the ghost rows allow it, single steps otherwise
+                const int adv = (h->tblock > 1 && h->valid_ghost >= h->tblock && nt - t >= h->tblock) ? h->tblock : 1;
+                auto upd = [&](int lo, int hi) { return adv > 1 ? update_rows_fused(h, lo, hi, h->s_compute) : update_rows(h, lo, hi, h->s_compute); };
+                const int e = h->valid_ghost - adv;   // ghost rows still valid after this advance
                 if (e == 0 && overlap) {
                     // edge strips first, then their exchange on s_comm behind the interior update
-                    CUDA_TRY(update_rows(h, own_lo, own_lo + h->g - 1, h->s_compute));
-                    CUDA_TRY(update_rows(h, own_hi - h->g + 1, own_hi, h->s_compute));
+                    CUDA_TRY(upd(own_lo, own_lo + h->g - 1));
+                    CUDA_TRY(upd(own_hi - h->g + 1, own_hi));
                     CUDA_TRY(cudaEventRecord(h->ev_boundary, h->s_compute));
                     CUDA_TRY(cudaStreamWaitEvent(h->s_comm, h->ev_boundary, 0));
                     rc = exchange(h, h->cur ^ 1, h->s_comm);
                     if (rc) return rc;
                     CUDA_TRY(cudaEventRecord(h->ev_comm, h->s_comm));
                     h->comm_pending = true;
-                    CUDA_TRY(update_rows(h, own_lo + h->g, own_hi - h->g, h->s_compute));
+                    CUDA_TRY(upd(own_lo + h->g, own_hi - h->g));
                     h->valid_ghost = h->g;
                 } else {
-                    CUDA_TRY(update_rows(h, own_lo - e, own_hi + e, h->s_compute));
+                    CUDA_TRY(upd(own_lo - e, own_hi + e));
                     h->valid_ghost = e;
                     if (e == 0) {
                         rc = exchange(h, h->cur ^ 1, h->s_compute);
@@ -495,6 +540,7 @@ int heat_step(heat_handle* h, int nt) {
                     }
                 }
                 h->cur ^= 1;
+                t += adv;
             }
             int rc = wait_comm(h);   // the timed region of this call ends after its last exchange
             if (rc) return rc;
