@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <pthread.h>
 #include <string>
 
 #include "kernels_basic.cuh"
@@ -664,3 +665,67 @@ int heat_get_timing(heat_handle* h, heat_timing* t) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------ no-allocation checksum
+// For callers that must not allocate device memory: a host program in the style of the reference's
+// Fortran drivers, which owns every device buffer itself and hands raw pointers to launchers; a
+// process whose device heap is already fully reserved by another allocator (a framework's caching
+// pool, an OpenACC/CUDA-Fortran runtime); or a time loop on several streams where cudaMalloc and
+// cudaFree would stall every stream because they synchronise the whole device.
+//
+// heat_checksum keeps its per-block partial sums in a buffer it cudaMallocs on first use.  This
+// variant runs the same two kernels with the partials in the fixed array below instead, so it never
+// calls cudaMalloc, cudaFree or anything else that allocates.  The price: the array is part of the
+// library image, so every GPU that loads libheat.so carries these 8 KiB until the process exits,
+// and the number of partial sums is capped at HEAT_NOALLOC_MAX_PARTIALS.
+#define HEAT_NOALLOC_MAX_PARTIALS 1024
+#define HEAT_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) double g_noalloc_partials[HEAT_NOALLOC_MAX_PARTIALS];
+
+// In host code `g_noalloc_partials` is only a handle for the symbol, not a device address, so the
+// address each device gives the array is looked up once per device with cudaGetSymbolAddress.
+static double* g_noalloc_addr[HEAT_NOALLOC_MAX_DEVICES];
+static bool g_noalloc_ready[HEAT_NOALLOC_MAX_DEVICES];
+static pthread_mutex_t g_noalloc_lock = PTHREAD_MUTEX_INITIALIZER;
+
+extern "C" int heat_checksum_noalloc(const void* field_dev, int dtype, int nx, int ny, int64_t pitch,
+                                     int nblocks, double* sum_dev, uint64_t stream) {
+    if (!field_dev || !sum_dev) return fail(HEAT_ERR_INVALID, "heat_checksum_noalloc: null pointer");
+    if (dtype != HEAT_F64 && dtype != HEAT_F32) return fail(HEAT_ERR_INVALID, "heat_checksum_noalloc: bad dtype %d", dtype);
+    if (nx < 1 || ny < 1 || pitch < nx)
+        return fail(HEAT_ERR_INVALID, "heat_checksum_noalloc: need nx, ny >= 1 and pitch >= nx (got %d x %d, pitch %lld)", nx, ny, (long long)pitch);
+    if (nblocks == 0) nblocks = kSumBlocks;      // the tree heat_checksum uses, hence the same bits
+    if (nblocks < 0 || nblocks > HEAT_NOALLOC_MAX_PARTIALS)
+        return fail(HEAT_ERR_UNSUPPORTED,
+                    "heat_checksum_noalloc: %d partial sums requested but the built-in scratch holds at most %d; "
+                    "use heat_checksum (which allocates) or fewer blocks", nblocks, HEAT_NOALLOC_MAX_PARTIALS);
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= HEAT_NOALLOC_MAX_DEVICES)
+        return fail(HEAT_ERR_UNSUPPORTED, "heat_checksum_noalloc: device ordinal %d is beyond the %d this build tracks", dev, HEAT_NOALLOC_MAX_DEVICES);
+    pthread_mutex_lock(&g_noalloc_lock);
+    if (!g_noalloc_ready[dev]) {                 // set-up: first call on this device, with it current
+        double* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_partials);
+        if (e != cudaSuccess || !p) {
+            pthread_mutex_unlock(&g_noalloc_lock);
+            return fail(HEAT_ERR_CUDA, "heat_checksum_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        }
+        g_noalloc_addr[dev] = p;
+        g_noalloc_ready[dev] = true;
+    }
+    double* partials = g_noalloc_addr[dev];
+    pthread_mutex_unlock(&g_noalloc_lock);
+    cudaStream_t s = (cudaStream_t)(uintptr_t)stream;
+    // Every slot the second kernel reads is written by the first one in this same call, so nothing
+    // left in the array by an earlier call matters and nothing has to be zeroed.
+    if (dtype == HEAT_F32)
+        heat_sum_partial_kernel<float><<<nblocks, 256, 0, s>>>((const float*)field_dev, nx, (long)pitch, 0, ny, partials);
+    else
+        heat_sum_partial_kernel<double><<<nblocks, 256, 0, s>>>((const double*)field_dev, nx, (long)pitch, 0, ny, partials);
+    CUDA_TRY(cudaGetLastError());
+    heat_sum_final_kernel<<<1, 32, 0, s>>>(partials, nblocks, sum_dev);
+    CUDA_TRY(cudaGetLastError());
+    return HEAT_OK;
+}

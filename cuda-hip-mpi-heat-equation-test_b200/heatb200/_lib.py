@@ -63,6 +63,8 @@ PROTOTYPES = {
     "heat_halo_exchange": (C.c_int, [_H]),
     "heat_gather": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_int]),
     "heat_checksum": (C.c_int, [_H, C.POINTER(C.c_double)]),
+    "heat_checksum_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
+                                        C.c_void_p, C.c_uint64]),
     "heat_sync": (C.c_int, [_H]),
     "heat_get_info": (C.c_int, [_H, C.POINTER(HeatInfo)]),
     "heat_get_timing": (C.c_int, [_H, C.POINTER(HeatTiming)]),

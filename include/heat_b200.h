@@ -134,6 +134,23 @@ int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root);
  * ref: the commented-out debug check fortran/mpi+cuda/heat.F90:266-273. */
 int heat_checksum(heat_handle* h, double* sum);
 
+/* No counterpart in the reference.  The checksum for callers that must not allocate device memory:
+ * programs that, like the reference's Fortran drivers, own every device buffer themselves and only
+ * pass raw pointers to launchers; processes whose device heap another allocator has already
+ * reserved; multi-stream time loops that cannot afford the device-wide synchronisation of
+ * cudaMalloc/cudaFree.  Sums the caller's DEVICE array field_dev ([ny][pitch] elements of `dtype`,
+ * nx cells used per row) into *sum_dev (DEVICE double), asynchronously on `stream` (a cudaStream_t,
+ * 0 = default stream), on the CURRENT device.  The per-block partial sums live in an 8 KiB array built
+ * into the library (held by every GPU that loads it until the process exits) instead of a
+ * cudaMalloc'ed buffer; the call performs no cudaMalloc/cudaFree and uses no allocating routine.
+ * nblocks = number of partial sums: 0 selects heat_checksum's own reduction tree (same bits);
+ * more than 1024 (the array's capacity) is refused with HEAT_ERR_UNSUPPORTED.  The first call on each
+ * device looks up the array's device address; make that call outside any stream capture.  All
+ * calls share the one array (whatever the previous call left in it is overwritten before it is read),
+ * so two calls that may overlap on the same GPU — different streams or threads — race: serialise them. */
+int heat_checksum_noalloc(const void* field_dev, int dtype, int nx, int ny, int64_t pitch,
+                          int nblocks, double* sum_dev, uint64_t stream);
+
 int heat_sync(heat_handle* h);
 int heat_get_info(heat_handle* h, heat_info* info);
 int heat_get_timing(heat_handle* h, heat_timing* t);
