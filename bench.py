@@ -228,11 +228,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt = torch.frombuffer(bytearray(heatb200.nccl_unique_id()), dtype=torch.uint8).cuda()
-        dist.broadcast(idt, 0)
-        nccl_id = bytes(idt.cpu().numpy().tobytes())
+        from heatb200 import dist as hdist
+        nccl_id = hdist.shared_nccl_id()     # rank 0: heat_nccl_unique_id(); broadcast over torch.distributed
 
     dtype = np.float64 if args.dtype == "f64" else np.float32
     esize = np.dtype(dtype).itemsize

@@ -1,0 +1,60 @@
+"""Host-side plumbing for row-slab runs with one process per GPU (replaces the MPI set-up of
+fortran/mpi+cuda/heat.F90:53-103).  torch.distributed only carries the 128-byte ncclUniqueId and test
+traffic; halo rows move inside libheat.so (ncclSend/ncclRecv), never through torch.
+Works with the `nccl` backend on GPUs and with `gloo` on CPUs (where heat_init then fails loudly).
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from . import solver as _solver
+
+
+def env_rank():
+    """(rank, world_size, local_rank) from the torchrun environment (defaults: single process)."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def broadcast_bytes(payload: bytes | None, nbytes: int, src: int = 0, device=None) -> bytes:
+    """Broadcast a fixed-size byte string from `src` over the default process group."""
+    import torch
+    import torch.distributed as dist
+    if device is None:
+        device = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    if dist.get_rank() == src:
+        if payload is None or len(payload) != nbytes:
+            raise ValueError("broadcast_bytes: source must supply exactly %d bytes" % nbytes)
+        t.copy_(torch.frombuffer(bytearray(payload), dtype=torch.uint8))
+    dist.broadcast(t, src)
+    return t.cpu().numpy().tobytes()
+
+
+def shared_nccl_id(make_id=_solver.nccl_unique_id) -> bytes:
+    """Rank 0 creates the ncclUniqueId (heat_nccl_unique_id), everyone receives it.
+    ref: MPI_Init + MPI_Cart_create, fortran/mpi+cuda/heat.F90:60-62,97."""
+    import torch.distributed as dist
+    payload = make_id() if dist.get_rank() == 0 else None
+    return broadcast_bytes(payload, 128, 0)
+
+
+def my_rows(ny: int):
+    """This rank's (row0, nrows) under the library's partition."""
+    import torch.distributed as dist
+    return _solver.slab_partition(ny, dist.get_world_size(), dist.get_rank())
+
+
+def slab_solver(field_slab: np.ndarray, ny_global: int, rx, ry=None, *, nccl_id: bytes | None = None,
+                device: int | None = None, **kw) -> "_solver.HeatSolver":
+    """HeatSolver for this rank's slab of a [ny_global, nx] field; collective."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if nccl_id is None and world > 1:
+        nccl_id = shared_nccl_id()
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    return _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
+                              device=device, **kw)

@@ -1,0 +1,72 @@
+"""Worker for tests/test_multi_gpu.py: run under torch.distributed.run with one rank per GPU.
+Each case marches a field decomposed into row slabs (NCCL halo exchange inside libheat.so) and compares the
+globally gathered result on rank 0, bit for bit, with the same march on one GPU and with the oracle."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "cuda-hip-mpi-heat-equation-test_b200")):
+    sys.path.insert(0, p)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import heatb200  # noqa: E402
+from heatb200 import dist as hd  # noqa: E402
+from oracle import heat_oracle as ho  # noqa: E402
+
+R100 = 0.24999999999999997
+
+
+def main():
+    rank, world, local = hd.env_rank()
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    nccl_id = hd.shared_nccl_id()
+    failures = []
+    cases = [
+        # (ny, nx, steps, ghost, overlap, tblock, kernel, dtype)
+        (64, 96, 9, 1, False, 1, "simple", np.float64),      # the reference's protocol: exchange every step
+        (64, 96, 9, 1, True, 1, "stream", np.float64),
+        (203, 130, 23, 4, True, 1, "tma", np.float64),       # ragged rows (203 % world != 0), deep halo
+        (203, 130, 23, 4, False, 2, "tma", np.float64),      # fused steps under a deep halo
+        (512, 1000, 40, 8, True, 4, "tma", np.float64),
+        (512, 1000, 37, 8, True, 2, "tma", np.float32),
+        (1024, 2048, 30, 16, True, 1, "tma", np.float64),
+    ]
+    for ci, (ny, nx, steps, g, overlap, k, kernel, dtype) in enumerate(cases):
+        full = (1.0 + np.random.default_rng(100 + ci).random((ny, nx))).astype(dtype)
+        r0, nr = hd.my_rows(ny)
+        s = hd.slab_solver(full[r0:r0 + nr], ny, R100, 0.2437, nccl_id=nccl_id, device=local, order="pyserial",
+                           kernel=kernel, tblock=k, ghost=g, overlap=overlap)
+        s.step(steps // 2)
+        s.step(steps - steps // 2)                 # split: exercises ghost state carried between calls
+        got = s.gather(root=0)
+        local_rows = s.gather()
+        ck = s.checksum()
+        t = s.timing()
+        s.close()
+        cks = torch.tensor([ck], dtype=torch.float64, device="cuda")
+        dist.all_reduce(cks)
+        if rank == 0:
+            want = ho.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437))
+            one = heatb200.march(full, steps, R100, 0.2437, order="pyserial", kernel=kernel, tblock=k, device=local)
+            ok = (np.array_equal(got.view(np.uint8), want.view(np.uint8)) and
+                  np.array_equal(got.view(np.uint8), one.view(np.uint8)) and
+                  np.array_equal(local_rows, want[r0:r0 + nr]) and
+                  abs(float(cks.item()) - float(want.astype(np.float64).sum())) <= 1e-9 * abs(float(want.sum())))
+            if not ok:
+                failures.append((ci, ny, nx, steps, g, overlap, k, kernel, str(dtype), int((got != want).sum())))
+            print("case %d %s exchanges=%d launches=%d" % (ci, "ok" if ok else "FAIL", t.halo_exchanges, t.kernel_launches), flush=True)
+    flag = torch.tensor([len(failures)], device="cuda")
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    if rank == 0 and failures:
+        print("FAILURES:", failures, flush=True)
+    sys.exit(1 if int(flag.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()
