@@ -209,6 +209,11 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args, wl)
 
+    # stdout carries exactly one JSON line: anything libraries print there (e.g. NCCL's version banner)
+    # is sent to stderr for the duration of the run
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import heatb200
     from heatb200 import config, ic
@@ -355,7 +360,8 @@ def main():
                 "value": g, "unit": UNIT, "cores": cores, "kind": "port",
                 "sample": "%dx%d fp64, %d timesteps in %.1f s: C port of the fortran/serial loop, OpenMP on %d cores" % (cnx, cnx, st, dt, cores),
                 "numpy_1thread": {"value": gn, "sample": "python/serial expression (heat.py:49-58) in NumPy, %dx%d, %d steps" % (cnx, cnx, stn)}}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -419,8 +419,6 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         h->owns = true;
         INIT_TRY(cudaMalloc(&h->buf[0], bytes));
         INIT_TRY(cudaMalloc(&h->buf[1], bytes));
-        INIT_TRY(cudaMemset(h->buf[0], 0, bytes));
-        INIT_TRY(cudaMemset(h->buf[1], 0, bytes));
     }
     if (cfg->stream) {
         h->s_compute = (cudaStream_t)(uintptr_t)cfg->stream;
@@ -433,6 +431,13 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     INIT_TRY(cudaStreamCreateWithPriority(&h->s_comm, cudaStreamNonBlocking, prio_hi));
     for (cudaEvent_t* e : {&h->ev_t0, &h->ev_t1, &h->ev_h0, &h->ev_h1}) INIT_TRY(cudaEventCreate(e));
     for (cudaEvent_t* e : {&h->ev_boundary, &h->ev_comm}) INIT_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    if (h->owns) {
+        // zero the pitch padding and ghost rows ON THE COMPUTE STREAM: s_compute is non-blocking, so a
+        // cudaMemset on the legacy default stream would not be ordered before the first field upload
+        const size_t bytes = (size_t)h->lrows * row_bytes(h);
+        INIT_TRY(cudaMemsetAsync(h->buf[0], 0, bytes, h->s_compute));
+        INIT_TRY(cudaMemsetAsync(h->buf[1], 0, bytes, h->s_compute));
+    }
 
     rc = resolve_kernel(h);
     if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
@@ -520,11 +525,15 @@ int heat_step(heat_handle* h, int nt) {
                 auto upd = [&](int lo, int hi) { return adv > 1 ? update_rows_fused(h, lo, hi, h->s_compute) : update_rows(h, lo, hi, h->s_compute); };
                 const int e = h->valid_ghost - adv;   // ghost rows still valid after this advance
                 if (e == 0 && overlap) {
-                    // edge strips first, then their exchange on s_comm behind the interior update
-                    CUDA_TRY(upd(own_lo, own_lo + h->g - 1));
-                    CUDA_TRY(upd(own_hi - h->g + 1, own_hi));
+                    // The two g-row edge strips and their exchange run on the high-priority stream s_comm,
+                    // concurrently with the interior update on s_compute: all three read buf[cur] and write
+                    // disjoint rows of buf[cur^1].  s_comm first waits for everything already queued on
+                    // s_compute (the previous steps, which wrote buf[cur]).
+                    auto upd_on = [&](int lo, int hi, cudaStream_t st) { return adv > 1 ? update_rows_fused(h, lo, hi, st) : update_rows(h, lo, hi, st); };
                     CUDA_TRY(cudaEventRecord(h->ev_boundary, h->s_compute));
                     CUDA_TRY(cudaStreamWaitEvent(h->s_comm, h->ev_boundary, 0));
+                    CUDA_TRY(upd_on(own_lo, own_lo + h->g - 1, h->s_comm));
+                    CUDA_TRY(upd_on(own_hi - h->g + 1, own_hi, h->s_comm));
                     rc = exchange(h, h->cur ^ 1, h->s_comm);
                     if (rc) return rc;
                     CUDA_TRY(cudaEventRecord(h->ev_comm, h->s_comm));

@@ -24,7 +24,6 @@ def main():
     rank, world, local = hd.env_rank()
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    nccl_id = hd.shared_nccl_id()
     failures = []
     cases = [
         # (ny, nx, steps, ghost, overlap, tblock, kernel, dtype)
@@ -39,6 +38,7 @@ def main():
     for ci, (ny, nx, steps, g, overlap, k, kernel, dtype) in enumerate(cases):
         full = (1.0 + np.random.default_rng(100 + ci).random((ny, nx))).astype(dtype)
         r0, nr = hd.my_rows(ny)
+        nccl_id = hd.shared_nccl_id()              # a ncclUniqueId serves exactly one communicator
         s = hd.slab_solver(full[r0:r0 + nr], ny, R100, 0.2437, nccl_id=nccl_id, device=local, order="pyserial",
                            kernel=kernel, tblock=k, ghost=g, overlap=overlap)
         s.step(steps // 2)
@@ -53,12 +53,18 @@ def main():
         if rank == 0:
             want = ho.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437))
             one = heatb200.march(full, steps, R100, 0.2437, order="pyserial", kernel=kernel, tblock=k, device=local)
-            ok = (np.array_equal(got.view(np.uint8), want.view(np.uint8)) and
-                  np.array_equal(got.view(np.uint8), one.view(np.uint8)) and
-                  np.array_equal(local_rows, want[r0:r0 + nr]) and
-                  abs(float(cks.item()) - float(want.astype(np.float64).sum())) <= 1e-9 * abs(float(want.sum())))
+            checks = {
+                "global_vs_oracle": np.array_equal(got.view(np.uint8), want.view(np.uint8)),
+                "global_vs_one_gpu": np.array_equal(got.view(np.uint8), one.view(np.uint8)),
+                "local_rows": np.array_equal(local_rows, want[r0:r0 + nr]),
+                "checksum": abs(float(cks.item()) - float(want.astype(np.float64).sum())) <= 1e-9 * abs(float(want.sum())),
+            }
+            ok = all(checks.values())
             if not ok:
-                failures.append((ci, ny, nx, steps, g, overlap, k, kernel, str(dtype), int((got != want).sum())))
+                failures.append((ci, ny, nx, steps, g, overlap, k, kernel, str(dtype), checks, float(cks.item()),
+                                 float(want.astype(np.float64).sum()),
+                                 "one!=want at %s" % np.argwhere(one != want)[:6].tolist(),
+                                 "local!=want at %s" % np.argwhere(local_rows != want[r0:r0 + nr])[:6].tolist()))
             print("case %d %s exchanges=%d launches=%d" % (ci, "ok" if ok else "FAIL", t.halo_exchanges, t.kernel_launches), flush=True)
     flag = torch.tensor([len(failures)], device="cuda")
     dist.broadcast(flag, 0)
