@@ -18,12 +18,14 @@
 // out-of-range box cells (zero-filled by TMA) and the strip's outer HX columns only ever feed
 // cells outside the region that is stored.
 #pragma once
+#include <type_traits>
+
 #include "kernels_tma.cuh"
 
 namespace heat {
 
 constexpr int kTempWarps = 4;     // warps per CTA (independent workers)
-constexpr int kTempRS = 4;        // rows per TMA stage
+constexpr int kTempRS = 3;        // rows per TMA stage == period of the register-row rotation
 constexpr int kTempStages = 4;    // stages in each warp's ring
 
 template <typename T, int K> struct TemporalGeom {
@@ -35,7 +37,7 @@ template <typename T, int ORDER, bool FMA, int K, int M>
 __global__ void __launch_bounds__(kTempWarps * 32)
 heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
                      int y_begin, int y_end, int seg_rows, int nstrips, int nitems, int ybc0, int ybc1,
-                     T rx, T ry) {
+                     T rx, T ry, int pdl_early) {
     constexpr int V = Pack<T>::V;
     using P = Pack<T>;
     constexpr int MV = M * V;                     // cells per lane
@@ -43,12 +45,14 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
     constexpr int HX = TemporalGeom<T, K>::HX;
     constexpr int WOUT = WIN - 2 * HX;            // strip width stored
     constexpr int RS = kTempRS, S = kTempStages;
+    static_assert(RS == 3, "the row rotation below has period 3");
     constexpr unsigned kStageBytes = RS * WIN * sizeof(T);
     static_assert(kStageBytes % 128 == 0, "stage alignment");
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * kTempWarps + warp;
+    if (pdl_early) pdl_launch_dependents();
     if (item >= nitems) return;                   // whole warps leave; nothing below syncs across warps
     const int strip = item % nstrips, seg = item / nstrips;
     const int xs = strip * WOUT - HX;             // first column of the loaded strip
@@ -69,6 +73,9 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
 #pragma unroll
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_fence_init();
+    }
+    pdl_wait();                                   // previous launch's field is complete and visible
+    if (lane == 0) {
         for (int j = 0; j < S && j < nst; ++j) issue(j);
     }
     __syncwarp();
@@ -82,74 +89,93 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
         any_fix |= colfix[i];
     }
     const bool warp_fix = __any_sync(0xffffffffu, any_fix);
+    bool st_ok[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        const int rel = lane * MV + m * V;
+        st_ok[m] = rel >= HX && rel < HX + WOUT && xl + m * V < pitch;
+    }
+    T* const out_base = dst + xl;
 
-    T prev1[K][MV], prev2[K][MV];                  // levels 0..K-1: rows y-1 and y-2 of the wavefront
+    // R[t][slot]: three consecutive rows of time level t (t = 0..K-1).  The roles south/centre/north
+    // rotate through the slots with period 3 == RS, so with the row loop unrolled by 3 every index is
+    // a compile-time constant and no register is ever copied.
+    T R[K][3][MV];
 #pragma unroll
     for (int t = 0; t < K; ++t)
 #pragma unroll
-        for (int i = 0; i < MV; ++i) prev1[t][i] = prev2[t][i] = T(0);
+        for (int b = 0; b < 3; ++b)
+#pragma unroll
+            for (int i = 0; i < MV; ++i) R[t][b][i] = T(0);
 
-    for (int p = 0; p < nin; ++p) {
-        const int j = p / RS, q = p % RS;
-        if (q == 0) mbar_wait(&full[j % S], (unsigned)((j / S) & 1));
-        T newest[MV];
-        {
-            const T* row = ring + (size_t)(j % S) * RS * WIN + (size_t)q * WIN + lane * MV;
+    // One stage = RS(=3) rows through all K levels.  FIX = this stage may touch Dirichlet cells (boundary
+    // columns in this warp's strip, or a boundary row within reach); only then are the pass-through
+    // selects compiled in.  Interior stages — almost all of them — run the select-free copy.
+    auto stage_rows = [&](auto fix_tag, const T* stage, int gy0) {
+        constexpr bool FIX = decltype(fix_tag)::value;
 #pragma unroll
-            for (int m = 0; m < M; ++m) {
-                const P v = *reinterpret_cast<const P*>(row + m * V);
+        for (int ph = 0; ph < 3; ++ph) {
+            const int so = ph % 3, ce = (ph + 1) % 3, no = (ph + 2) % 3;   // slots: south, centre, north
+            {
+                const T* row = stage + ph * WIN;
 #pragma unroll
-                for (int i = 0; i < V; ++i) newest[m * V + i] = v.v[i];
+                for (int m = 0; m < M; ++m) {
+                    const P v = *reinterpret_cast<const P*>(row + m * V);
+#pragma unroll
+                    for (int i = 0; i < V; ++i) R[0][no][m * V + i] = v.v[i];
+                }
             }
-        }
-        const int gy = ys - K + p;                 // level-0 row that just arrived
+            const int gy = gy0 + ph;               // level-0 row that just arrived
+            T outrow[MV];
 #pragma unroll
-        for (int t = 1; t <= K; ++t) {
-            const int r = gy - t;                  // level-t row produced now
-            T (&c)[MV] = prev1[t - 1];
-            T (&s)[MV] = prev2[t - 1];
-            const T left = __shfl_up_sync(0xffffffffu, c[MV - 1], 1);
-            const T right = __shfl_down_sync(0xffffffffu, c[0], 1);
-            const bool rowfix = (r == ybc0) || (r == ybc1);
-            T nw[MV];
+            for (int t = 1; t <= K; ++t) {
+                const T* c = R[t - 1][ce];
+                const T* s = R[t - 1][so];
+                const T* n = R[t - 1][no];
+                T* nw = (t < K) ? R[t < K ? t : 0][no] : outrow;
+                const T left = __shfl_up_sync(0xffffffffu, c[MV - 1], 1);
+                const T right = __shfl_down_sync(0xffffffffu, c[0], 1);
 #pragma unroll
-            for (int i = 0; i < MV; ++i) {
-                const T w = (i == 0) ? left : c[i - 1];
-                const T e = (i == MV - 1) ? right : c[i + 1];
-                nw[i] = stencil<T, ORDER, FMA>(c[i], w, e, s[i], newest[i], rx, ry);
+                for (int i = 0; i < MV; ++i) {
+                    const T w = (i == 0) ? left : c[i - 1];
+                    const T e = (i == MV - 1) ? right : c[i + 1];
+                    nw[i] = stencil<T, ORDER, FMA>(c[i], w, e, s[i], n[i], rx, ry);
+                }
+                if constexpr (FIX) {
+                    const int r = gy - t;          // level-t row produced now
+                    const bool rowfix = (r == ybc0) || (r == ybc1);
+#pragma unroll
+                    for (int i = 0; i < MV; ++i) nw[i] = (rowfix || colfix[i]) ? c[i] : nw[i];
+                }
             }
-            if (rowfix) {
+            const int o = gy - K;                  // level-K row, complete
+            if (o >= ys && o < ye) {
+                T* orow = out_base + (long)o * pitch;
 #pragma unroll
-                for (int i = 0; i < MV; ++i) nw[i] = c[i];
-            } else if (warp_fix) {
+                for (int m = 0; m < M; ++m) {
+                    if (st_ok[m]) {
+                        P out;
 #pragma unroll
-                for (int i = 0; i < MV; ++i) nw[i] = colfix[i] ? c[i] : nw[i];
-            }
-#pragma unroll
-            for (int i = 0; i < MV; ++i) {
-                s[i] = c[i];
-                c[i] = newest[i];
-                newest[i] = nw[i];
-            }
-        }
-        const int o = gy - K;                      // level-K row, complete
-        if (o >= ys && o < ye) {
-#pragma unroll
-            for (int m = 0; m < M; ++m) {
-                const int rel = lane * MV + m * V;
-                if (rel >= HX && rel < HX + WOUT && xl + m * V < pitch) {
-                    P out;
-#pragma unroll
-                    for (int i = 0; i < V; ++i) out.v[i] = newest[m * V + i];
-                    *reinterpret_cast<P*>(dst + (long)o * pitch + xl + m * V) = out;
+                        for (int i = 0; i < V; ++i) out.v[i] = outrow[m * V + i];
+                        *reinterpret_cast<P*>(orow + m * V) = out;
+                    }
                 }
             }
         }
-        if (q == RS - 1) {                         // stage j fully consumed (its values are in registers)
-            __syncwarp();
-            if (lane == 0 && j + S < nst) issue(j + S);
-        }
+    };
+
+    for (int j = 0; j < nst; ++j) {
+        mbar_wait(&full[j % S], (unsigned)((j / S) & 1));
+        const T* stage = ring + (size_t)(j % S) * RS * WIN + lane * MV;
+        const int gy0 = ys - K + j * RS;
+        // rows produced by this stage span gy0-K .. gy0+RS-2
+        const bool fix = warp_fix || (ybc0 >= gy0 - K && ybc0 <= gy0 + RS) || (ybc1 >= gy0 - K && ybc1 <= gy0 + RS);
+        if (fix) stage_rows(std::true_type{}, stage, gy0);
+        else stage_rows(std::false_type{}, stage, gy0);
+        __syncwarp();                              // stage j fully consumed (its values are in registers)
+        if (lane == 0 && j + S < nst) issue(j + S);
     }
+    if (!pdl_early) pdl_launch_dependents();
 }
 
 // ------------------------------------------------------------------------------------ host side
@@ -199,9 +225,11 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     const int nsegs = (rows + seg - 1) / seg;
     const int nitems = nstrips * nsegs;
     const int grid = (nitems + kTempWarps - 1) / kTempWarps;
-    k<<<grid, kTempWarps * 32, smem, s>>>(st.map[which], dst, nx, pitch, yb, ye, seg, nstrips, nitems, ybc0, ybc1,
-                                          rx, ry);
-    return cudaGetLastError();
+    // signal dependents at CTA start only when the grid spans several waves: early-placed CTAs of the next
+    // launch would otherwise skew the balance of a grid that does not even fill the machine once
+    const int pdl_early = grid >= 2 * sm_count * 4 ? 1 : 0;
+    return launch_pdl(k, dim3(grid), dim3(kTempWarps * 32), smem, s, st.map[which], dst, nx, pitch, yb, ye, seg,
+                      nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early);
 }
 
 }  // namespace heat

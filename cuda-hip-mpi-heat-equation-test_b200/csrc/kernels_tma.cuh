@@ -59,6 +59,33 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(cx), "r"(cy), "r"(smem_u32(bar)) : "memory");
 }
 
+// Programmatic dependent launch: consecutive time steps are separate launches whose only true
+// dependency is the field itself.  A step's CTAs may be scheduled while the previous step's last
+// wave drains (launch_dependents is signalled at CTA start); they set up their barriers, then block
+// in griddepcontrol.wait until the previous grid has completed and flushed before touching memory.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static const bool on = [] { const char* v = getenv("HEAT_PDL"); return !(v && v[0] == '0'); }();
+    return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 template <typename T, int ORDER, bool FMA>
 __global__ void __launch_bounds__(kTmaThreads)
 heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
@@ -88,12 +115,14 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
     const int np = ye - ys;                         // centres p = 1..np  (global row ys-1+p)
     const int nstages = (np + 2 + BY - 1) / BY;     // input rows p = 0..np+1
 
+    pdl_launch_dependents();
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_fence_init();
     }
     __syncthreads();
+    pdl_wait();                                     // previous step's field is complete and visible
 
     auto issue = [&](int j) {
         const int slot = j % S;
@@ -227,8 +256,7 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     }
     seg = std::min(seg, rows);
     const int gy = (rows + seg - 1) / seg;
-    k<<<dim3(gx, gy), kTmaThreads, smem, s>>>(st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry);
-    return cudaGetLastError();
+    return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry);
 }
 
 }  // namespace heat
