@@ -310,8 +310,14 @@ def main():
     bytes_per_lup = 2 * esize / max(args.tblock, 1)
     achieved = local_lups_per_launch * bytes_per_lup / (avg_kernel_ms * 1e-3) / 1e9
     peak, peak_src = peaks()
+    traffic = None
+    try:      # measured DRAM bytes per launch of this kernel/config, from the committed ncu capture (if one exists)
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get("%s:%s:%s:k%d" % (args.workload, solver.kernel_name, args.dtype, max(args.tblock, 1)))
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": solver.kernel_name,
+                "traffic": traffic, "algorithmic_bytes_per_launch": local_lups_per_launch * bytes_per_lup, "peak_source": peak_src, "kernel": solver.kernel_name,
                 "algorithmic_bytes_per_lup": bytes_per_lup, "avg_kernel_ms": avg_kernel_ms,
                 "glups_roof": peak / bytes_per_lup,
                 "effective_gbs_at_single_step_traffic": achieved * max(args.tblock, 1)}

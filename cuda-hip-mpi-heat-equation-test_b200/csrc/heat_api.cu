@@ -119,6 +119,10 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
         const int gy = (rows + rpb - 1) / rpb;
         heat_stream_kernel<T, ORDER, FMA, 4><<<dim3(gx, gy), threads, 0, s>>>(
             S, D, h->nx, h->pitch, yb, ye, rpb, rx, ry);
+    } else if (h->kernel == HEAT_KERNEL_WTMA) {
+        const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;
+        return launch_temporal_rows<T, ORDER, FMA, 1>(h->temporal, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch, yb, ye,
+                                                     ybc0, ybc1, rx, ry, h->sm_count, s);
     } else if (h->kernel == HEAT_KERNEL_TMA) {
         return launch_tma_rows<T, ORDER, FMA>(h->tma, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch,
                                               yb, ye, rx, ry, h->sm_count, s);
@@ -246,14 +250,16 @@ static int resolve_kernel(heat_handle* h) {
     int k = c.kernel;
     if (k == HEAT_KERNEL_AUTO) {
         if (fits_resident) k = HEAT_KERNEL_RESIDENT;
-        else if (aligned) k = HEAT_KERNEL_TMA;      // measured fastest at 4096^2 and 16384^2 (profiles/)
+        else if (aligned)                            // measured (profiles/): fp64 -> CTA-level TMA kernel at 4096^2 and
+            k = (c.dtype == HEAT_F32 && (long)h->nx * h->lrows >= (1L << 26)) ? HEAT_KERNEL_WTMA   // 16384^2; large fp32 ->
+                                                                               : HEAT_KERNEL_TMA;  // warp-level pipelines
         else k = HEAT_KERNEL_SIMPLE;
     }
     if (k == HEAT_KERNEL_RESIDENT && !fits_resident)
         return fail(HEAT_ERR_UNSUPPORTED, "RESIDENT kernel needs nranks == 1 and 2*nx*ny*sizeof(T) <= 200 KiB");
-    if ((k == HEAT_KERNEL_STREAM || k == HEAT_KERNEL_TMA) && !aligned)
+    if ((k == HEAT_KERNEL_STREAM || k == HEAT_KERNEL_TMA || k == HEAT_KERNEL_WTMA) && !aligned)
         return fail(HEAT_ERR_UNSUPPORTED, "STREAM/TMA kernels need 16-byte aligned buffers and a pitch that is a multiple of %d elements", (int)V);
-    if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_RESIDENT) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
+    if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_WTMA) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
     h->kernel = k;
     return HEAT_OK;
 }
@@ -446,8 +452,8 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
     }
 
-    if (h->tblock > 1) {
-        if (h->tblock != 2 && h->tblock != 4) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: tblock must be 1, 2 or 4"); }
+    if (h->tblock > 1 || h->kernel == HEAT_KERNEL_WTMA) {
+        if (h->tblock != 1 && h->tblock != 2 && h->tblock != 4) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: tblock must be 1, 2 or 4"); }
         if (h->kernel == HEAT_KERNEL_SIMPLE || h->kernel == HEAT_KERNEL_RESIDENT) {
             h->tblock = 1;             // unaligned caller buffers / tiny fields: fall back to single steps
         } else {

@@ -14,12 +14,12 @@ LIB_PATH = os.path.join(HERE, "libheat.so")
 HEAT_OK, ERR_INVALID, ERR_CUDA, ERR_NCCL, ERR_NOMEM, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 F64, F32 = 0, 1
 ORDER_FORTRAN, ORDER_PYCUDA, ORDER_PYSERIAL = 0, 1, 2
-KERNEL_AUTO, KERNEL_SIMPLE, KERNEL_STREAM, KERNEL_TMA, KERNEL_RESIDENT = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_SIMPLE, KERNEL_STREAM, KERNEL_TMA, KERNEL_RESIDENT, KERNEL_WTMA = 0, 1, 2, 3, 4, 5
 FLAG_FMAD, FLAG_OVERLAP, FLAG_SKIP_EXCHANGE, FLAG_PEER_HALO = 1, 2, 4, 8
 
 ORDERS = {"fortran": ORDER_FORTRAN, "pycuda": ORDER_PYCUDA, "pyserial": ORDER_PYSERIAL}
 KERNELS = {"auto": KERNEL_AUTO, "simple": KERNEL_SIMPLE, "stream": KERNEL_STREAM, "tma": KERNEL_TMA,
-           "resident": KERNEL_RESIDENT}
+           "resident": KERNEL_RESIDENT, "wtma": KERNEL_WTMA}
 KERNEL_NAMES = {v: k for k, v in KERNELS.items()}
 
 

@@ -51,6 +51,8 @@ extern "C" {
 #define HEAT_KERNEL_STREAM  2   /* 128-bit row loads, register row window, shuffle neighbours    */
 #define HEAT_KERNEL_TMA     3   /* TMA 2-D tile loads (1-cell halo) into shared memory, mbarrier */
 #define HEAT_KERNEL_RESIDENT 4  /* whole field in one CTA's shared memory, all steps in 1 launch */
+#define HEAT_KERNEL_WTMA    5   /* one private TMA pipeline per WARP, rows rotate through registers
+                                   (the temporal-blocking kernel, also used for single steps)     */
 
 /* flags */
 #define HEAT_FLAG_FMAD          1u  /* allow FMA contraction (faster, <=1e-12 rel. off the oracle); default is

@@ -10,7 +10,7 @@ from oracle import c_oracle, heat_oracle as ho
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = ["simple", "stream", "tma"]
+KERNELS = ["simple", "stream", "tma", "wtma"]
 ORDERS = ["fortran", "pycuda", "pyserial"]
 R100 = 0.24999999999999997          # r for n = 100 (fortran/mpi+cuda/input.dat): not a power of two
 
