@@ -198,6 +198,7 @@ def main():
     ap.add_argument("--ghost", type=int, default=int(os.environ.get("HEAT_BENCH_GHOST", "16")))
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--skip-exchange", action="store_true", help="diagnostic: no halo traffic (results wrong)")
+    ap.add_argument("--peer-halo", action="store_true", help="halo rows by CUDA-IPC peer copies instead of NCCL")
     ap.add_argument("--timesteps", type=int, default=0, help="override time steps per bench step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -264,10 +265,12 @@ def main():
     tstream = torch.cuda.Stream()
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
-    solver = heatb200.HeatSolver(host_in, r, order="fortran", kernel=args.kernel, tblock=args.tblock, fmad=args.fmad,
-                                 device=local, rank=rank, nranks=world, ny=ny_global, ghost=(args.ghost if world > 1 else 0),
-                                 overlap=not args.no_overlap, skip_exchange=args.skip_exchange, nccl_id=nccl_id,
-                                 stream=stream)
+    common = dict(order="fortran", kernel=args.kernel, tblock=args.tblock, fmad=args.fmad, device=local, stream=stream)
+    if world > 1:
+        solver = hdist.slab_solver(host_in, ny_global, r, nccl_id=nccl_id, ghost=args.ghost, overlap=not args.no_overlap,
+                                   skip_exchange=args.skip_exchange, peer_halo=args.peer_halo, **common)
+    else:
+        solver = heatb200.HeatSolver(host_in, r, **common)
     lups_per_step = (nx - 2) * (ny_global - 2) * timesteps      # whole job, all ranks
 
     def barrier():
@@ -351,7 +354,7 @@ def main():
             "config": {"workload": args.workload + ": " + wl["desc"], "nx": nx, "ny_global": ny_global,
                        "timesteps_per_step": timesteps, "kernel": roofline["kernel"], "tblock": args.tblock,
                        "fmad": bool(args.fmad), "op_order": "fortran",
-                       "parallelism": "row-slabs x%d" % world + (", ghost %d, overlap %s" % (args.ghost, not args.no_overlap) if world > 1 else ""),
+                       "parallelism": "row-slabs x%d" % world + (", ghost %d, overlap %s, halo via %s" % (args.ghost, not args.no_overlap, "peer copies (CUDA IPC)" if args.peer_halo else "NCCL send/recv") if world > 1 else ""),
                        "l2": "working set %.0f MB per GPU vs 126 MB L2: inputs larger than L2, no flush" % (2 * nrows * nx * esize / 1e6)},
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(total_launches),
             "clocks": clk.summary(),

@@ -80,6 +80,15 @@ struct heat_handle {
     size_t stage_bytes = 0;
     TmaState tma;                  // tensor maps for the TMA kernels (kernels_tma.cuh)
     TemporalState temporal;        // tensor maps for the fused K-step kernel (kernels_temporal.cuh)
+    // peer-memory halo (HEAT_FLAG_PEER_HALO): neighbours' buffers and flag words mapped through CUDA IPC
+    uint32_t* d_flags = nullptr;   // own: [0] ready_from_up [1] ready_from_down [2] done_from_up [3] done_from_down
+    void* up_buf[2] = {nullptr, nullptr};
+    void* down_buf[2] = {nullptr, nullptr};
+    uint32_t* up_flags = nullptr;
+    uint32_t* down_flags = nullptr;
+    int up_nrows = 0;
+    bool peer_ready = false, peer_pending_fill = false;
+    uint32_t epoch = 0;
     int sm_count = 148;
     int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
     uint64_t steps_total = 0, launches = 0, exchanges = 0;
@@ -207,10 +216,74 @@ static cudaError_t update_rows_fused(heat_handle* h, int glo, int ghi, cudaStrea
 // Row slabs along the slow index make every halo a contiguous block of g rows, so NCCL reads the
 // field rows and writes the neighbour's ghost rows directly: no pack/unpack kernels and no staging
 // (contrast fortran/mpi+cuda/heat.F90:153-159,163-168,175-190).
+//
+// HEAT_FLAG_PEER_HALO replaces NCCL by the GPU's copy engines writing straight into the neighbour's ghost
+// rows (its buffers are mapped here through CUDA IPC), so no SM runs communication code at all.  Ordering
+// between the two processes uses one 32-bit flag word per direction in each GPU's memory and only
+// stream-ordered operations — a 1-thread kernel stores the epoch into the neighbour's flag, the receiving
+// stream blocks in cuStreamWaitValue32 on its own flag — never a kernel that spins on another GPU:
+//   ready: "every earlier kernel of mine that touches these ghost rows is done — you may overwrite them"
+//   done : "my rows have landed in your ghost rows"
+__global__ void heat_signal_kernel(uint32_t* a, uint32_t* b, uint32_t v) {
+    if (a) *reinterpret_cast<volatile uint32_t*>(a) = v;
+    if (b) *reinterpret_cast<volatile uint32_t*>(b) = v;
+    __threadfence_system();
+}
+
+typedef CUresult (*PFN_streamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static PFN_streamWaitValue32 get_wait_value32() {
+    static PFN_streamWaitValue32 fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (PFN_streamWaitValue32)p;
+    }();
+    return fn;
+}
+
+static int exchange_peer(heat_handle* h, int which, cudaStream_t s) {
+    PFN_streamWaitValue32 wait32 = get_wait_value32();
+    if (!wait32) return fail(HEAT_ERR_UNSUPPORTED, "peer halo: cuStreamWaitValue32 is not available from this driver");
+    const uint32_t epoch = ++h->epoch;
+    const bool up = h->cfg.rank > 0, down = h->cfg.rank + 1 < h->cfg.nranks;
+    const size_t bytes = (size_t)h->g * row_bytes(h);
+    auto wait_flag = [&](int idx) -> int {
+        CUresult r = wait32((CUstream)s, (CUdeviceptr)(uintptr_t)(h->d_flags + idx), epoch, CU_STREAM_WAIT_VALUE_GEQ);
+        if (r != CUDA_SUCCESS) return fail(HEAT_ERR_CUDA, "cuStreamWaitValue32 failed with CUresult %d", (int)r);
+        return HEAT_OK;
+    };
+    CUDA_TRY(cudaEventRecord(h->ev_h0, s));
+    // I am the up neighbour's "down" and the down neighbour's "up"
+    heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 1 : nullptr, down ? h->down_flags + 0 : nullptr, epoch);
+    CUDA_TRY(cudaGetLastError());
+    int rc;
+    if (up && (rc = wait_flag(0))) return rc;
+    if (down && (rc = wait_flag(1))) return rc;
+    if (up)     // my first g rows -> the bottom ghost rows of the rank above
+        CUDA_TRY(cudaMemcpyAsync((char*)h->up_buf[which] + (size_t)(h->g + h->up_nrows) * row_bytes(h),
+                                 row_ptr(h, which, h->g), bytes, cudaMemcpyDeviceToDevice, s));
+    if (down)   // my last g rows -> the top ghost rows of the rank below
+        CUDA_TRY(cudaMemcpyAsync((char*)h->down_buf[which], row_ptr(h, which, h->nrows), bytes,
+                                 cudaMemcpyDeviceToDevice, s));
+    heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 3 : nullptr, down ? h->down_flags + 2 : nullptr, epoch);
+    CUDA_TRY(cudaGetLastError());
+    if (up && (rc = wait_flag(2))) return rc;
+    if (down && (rc = wait_flag(3))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev_h1, s));
+    h->halo_timed = true;
+    return HEAT_OK;
+}
+
 static int exchange(heat_handle* h, int which, cudaStream_t s) {
     if (h->cfg.nranks <= 1) return HEAT_OK;
     h->exchanges++;
     if (h->cfg.flags & HEAT_FLAG_SKIP_EXCHANGE) return HEAT_OK;
+    if (h->cfg.flags & HEAT_FLAG_PEER_HALO) {
+        if (!h->peer_ready) return fail(HEAT_ERR_INVALID, "peer halo: call heat_peer_attach on every rank before stepping");
+        return exchange_peer(h, which, s);
+    }
     const NcclApi& N = nccl_api();
     const size_t count = (size_t)h->g * h->pitch;
     const int dt = h->cfg.dtype == HEAT_F32 ? ncclFloat32 : ncclFloat64;
@@ -314,6 +387,9 @@ int heat_destroy(heat_handle* h) {
     if (h->s_compute) cudaStreamSynchronize(h->s_compute);
     if (h->s_comm) cudaStreamSynchronize(h->s_comm);
     if (h->comm) nccl_api().CommDestroy(h->comm);
+    for (void* p : {h->up_buf[0], h->up_buf[1], h->down_buf[0], h->down_buf[1], (void*)h->up_flags, (void*)h->down_flags})
+        if (p) cudaIpcCloseMemHandle(p);
+    cudaFree(h->d_flags);
     if (h->owns) { cudaFree(h->buf[0]); cudaFree(h->buf[1]); }
     cudaFree(h->d_partials);
     cudaFree(h->d_sum);
@@ -341,7 +417,9 @@ int heat_set_field(heat_handle* h, const void* src, int64_t src_pitch, int src_i
                              cudaMemcpyDeviceToDevice, h->s_compute));
     h->cur = 0;
     h->valid_ghost = 0;
-    if (h->cfg.nranks > 1) {
+    if (h->cfg.nranks > 1 && (h->cfg.flags & HEAT_FLAG_PEER_HALO) && !h->peer_ready) {
+        h->peer_pending_fill = true;               // ghosts are filled by heat_peer_attach
+    } else if (h->cfg.nranks > 1) {
         // fill both buffers' ghosts so that the Dirichlet/ghost rows agree in both (collective)
         for (int b = 0; b < 2; ++b) {
             rc = exchange(h, b, h->s_compute);
@@ -365,8 +443,8 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks)
         return fail(HEAT_ERR_INVALID, "heat_init: bad rank %d of %d", cfg->rank, cfg->nranks);
     if (cfg->tblock < 0 || cfg->tblock > 8) return fail(HEAT_ERR_INVALID, "heat_init: tblock must be in 0..8");
-    if (cfg->nranks > 1 && !cfg->nccl_id && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE))
-        return fail(HEAT_ERR_INVALID, "heat_init: nranks > 1 needs cfg.nccl_id");
+    if (cfg->nranks > 1 && !cfg->nccl_id && !(cfg->flags & (HEAT_FLAG_SKIP_EXCHANGE | HEAT_FLAG_PEER_HALO)))
+        return fail(HEAT_ERR_INVALID, "heat_init: nranks > 1 needs cfg.nccl_id (or HEAT_FLAG_PEER_HALO)");
     if ((cfg->ext_buf[0] == nullptr) != (cfg->ext_buf[1] == nullptr))
         return fail(HEAT_ERR_INVALID, "heat_init: supply both ext_buf pointers or neither");
 
@@ -462,7 +540,13 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         }
     }
 
-    if (cfg->nranks > 1 && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE)) {
+    if (cfg->nranks > 1 && (cfg->flags & HEAT_FLAG_PEER_HALO)) {
+        if (!h->owns) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: peer halo needs library-owned buffers (CUDA IPC handles)"); }
+        INIT_TRY(cudaMalloc(&h->d_flags, 4 * sizeof(uint32_t)));
+        INIT_TRY(cudaMemsetAsync(h->d_flags, 0, 4 * sizeof(uint32_t), h->s_compute));
+        INIT_TRY(cudaStreamSynchronize(h->s_compute));
+    }
+    if (cfg->nranks > 1 && !(cfg->flags & HEAT_FLAG_SKIP_EXCHANGE) && cfg->nccl_id) {
         const NcclApi& N = nccl_api();
         if (!N.ok) { heat_destroy(h); return fail(HEAT_ERR_NCCL, "heat_init: NCCL not available (libnccl.so.2 could not be loaded)"); }
         ncclUniqueId id;
@@ -481,6 +565,63 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     *out = h;
     return HEAT_OK;
 #undef INIT_TRY
+}
+
+struct PeerBlob {                      // what one rank tells its neighbours (fits HEAT_PEER_BLOB_BYTES)
+    cudaIpcMemHandle_t buf[2];
+    cudaIpcMemHandle_t flags;
+    int32_t rank, nrows, ghost, dtype;
+    int64_t pitch;
+};
+static_assert(sizeof(PeerBlob) <= 256, "PeerBlob must fit HEAT_PEER_BLOB_BYTES");
+
+int heat_peer_export(heat_handle* h, void* blob) {
+    if (!h || !blob) return fail(HEAT_ERR_INVALID, "heat_peer_export: null argument");
+    if (!(h->cfg.flags & HEAT_FLAG_PEER_HALO) || !h->d_flags)
+        return fail(HEAT_ERR_INVALID, "heat_peer_export: handle was not created with HEAT_FLAG_PEER_HALO and nranks > 1");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    PeerBlob b;
+    memset(&b, 0, sizeof b);
+    CUDA_TRY(cudaIpcGetMemHandle(&b.buf[0], h->buf[0]));
+    CUDA_TRY(cudaIpcGetMemHandle(&b.buf[1], h->buf[1]));
+    CUDA_TRY(cudaIpcGetMemHandle(&b.flags, h->d_flags));
+    b.rank = h->cfg.rank; b.nrows = h->nrows; b.ghost = h->g; b.dtype = h->cfg.dtype; b.pitch = h->pitch;
+    memset(blob, 0, 256);
+    memcpy(blob, &b, sizeof b);
+    return HEAT_OK;
+}
+
+int heat_peer_attach(heat_handle* h, const void* up_blob, const void* down_blob) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_peer_attach: null handle");
+    if (!(h->cfg.flags & HEAT_FLAG_PEER_HALO) || !h->d_flags)
+        return fail(HEAT_ERR_INVALID, "heat_peer_attach: handle was not created with HEAT_FLAG_PEER_HALO and nranks > 1");
+    const bool up = h->cfg.rank > 0, down = h->cfg.rank + 1 < h->cfg.nranks;
+    if ((up && !up_blob) || (down && !down_blob)) return fail(HEAT_ERR_INVALID, "heat_peer_attach: missing neighbour blob");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    auto open_one = [&](const void* blob, int want_rank, void* bufs[2], uint32_t** flags, int* nrows) -> int {
+        PeerBlob b;
+        memcpy(&b, blob, sizeof b);
+        if (b.rank != want_rank || b.ghost != h->g || b.pitch != h->pitch || b.dtype != h->cfg.dtype)
+            return fail(HEAT_ERR_INVALID, "heat_peer_attach: blob of rank %d (ghost %d, pitch %lld) does not match neighbour %d (ghost %d, pitch %ld)",
+                        b.rank, b.ghost, (long long)b.pitch, want_rank, h->g, h->pitch);
+        for (int i = 0; i < 2; ++i) CUDA_TRY(cudaIpcOpenMemHandle(&bufs[i], b.buf[i], cudaIpcMemLazyEnablePeerAccess));
+        void* f = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&f, b.flags, cudaIpcMemLazyEnablePeerAccess));
+        *flags = (uint32_t*)f;
+        if (nrows) *nrows = b.nrows;
+        return HEAT_OK;
+    };
+    int rc;
+    if (up && (rc = open_one(up_blob, h->cfg.rank - 1, h->up_buf, &h->up_flags, &h->up_nrows))) return rc;
+    if (down && (rc = open_one(down_blob, h->cfg.rank + 1, h->down_buf, &h->down_flags, nullptr))) return rc;
+    h->peer_ready = true;
+    // first ghost fill (collective): both buffers, as heat_set_field does on the NCCL path
+    for (int b = 0; b < 2; ++b)
+        if ((rc = exchange(h, b, h->s_compute))) return rc;
+    h->valid_ghost = h->g;
+    h->peer_pending_fill = false;
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    return HEAT_OK;
 }
 
 int heat_halo_exchange(heat_handle* h) {

@@ -61,6 +61,8 @@ PROTOTYPES = {
     "heat_set_field": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int]),
     "heat_step": (C.c_int, [_H, C.c_int]),
     "heat_halo_exchange": (C.c_int, [_H]),
+    "heat_peer_export": (C.c_int, [_H, C.c_void_p]),
+    "heat_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
     "heat_gather": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_int]),
     "heat_checksum": (C.c_int, [_H, C.POINTER(C.c_double)]),
     "heat_checksum_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,

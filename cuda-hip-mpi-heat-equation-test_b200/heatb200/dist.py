@@ -56,5 +56,11 @@ def slab_solver(field_slab: np.ndarray, ny_global: int, rx, ry=None, *, nccl_id:
         nccl_id = shared_nccl_id()
     if device is None:
         device = int(os.environ.get("LOCAL_RANK", "0"))
-    return _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
-                              device=device, **kw)
+    s = _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
+                           device=device, **kw)
+    if kw.get("peer_halo") and world > 1:
+        # every rank publishes its CUDA-IPC blob; each takes its two neighbours' (replaces MPI_Cart_shift, :103)
+        blobs = [None] * world
+        dist.all_gather_object(blobs, s.peer_export())
+        s.peer_attach(blobs[rank - 1] if rank > 0 else None, blobs[rank + 1] if rank + 1 < world else None)
+    return s

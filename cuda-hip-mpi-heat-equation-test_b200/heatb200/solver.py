@@ -116,6 +116,18 @@ class HeatSolver:
         field = np.ascontiguousarray(field, dtype=self.dtype)
         check(lib().heat_set_field(self._h, field.ctypes.data_as(C.c_void_p), field.shape[1], 0))
 
+    def peer_export(self) -> bytes:
+        """This rank's CUDA-IPC blob (buffers + flag words) for its neighbours (peer_halo=True only)."""
+        buf = C.create_string_buffer(256)
+        check(lib().heat_peer_export(self._h, buf))
+        return buf.raw
+
+    def peer_attach(self, up_blob: bytes | None, down_blob: bytes | None) -> None:
+        """Map the neighbours' buffers and fill the ghosts (collective)."""
+        ub = C.create_string_buffer(up_blob, 256) if up_blob else None
+        db = C.create_string_buffer(down_blob, 256) if down_blob else None
+        check(lib().heat_peer_attach(self._h, ub, db))
+
     # ------------------------------------------------------------------ extras
     def gather_into_tensor(self, t) -> None:
         """Copy this rank's rows into a contiguous torch CUDA tensor [nrows, nx] (device to device)."""

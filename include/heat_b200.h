@@ -126,6 +126,17 @@ int heat_step(heat_handle* h, int nt);
  * ref: swap(), fortran/mpi+cuda/heat.F90:145-193; launch_send/recv1/recv2 heat_kernel.cpp:63-150. */
 int heat_halo_exchange(heat_handle* h);
 
+/* Peer-memory halo (HEAT_FLAG_PEER_HALO, one process per GPU on one NVLink node): instead of NCCL, each
+ * rank's copy engine writes its edge rows straight into the neighbours' ghost rows, which are mapped here
+ * through CUDA IPC; ordering uses flag words and stream-ordered waits only.  After heat_init every rank calls
+ * heat_peer_export(blob) (HEAT_PEER_BLOB_BYTES bytes), the host layer hands each rank the blobs of rank-1 and
+ * rank+1 (NULL at the ends), and heat_peer_attach opens them and performs the first ghost fill (collective).
+ * cfg.nccl_id may then be NULL (heat_gather with global_root >= 0 still needs it).
+ * ref: replaces swap() — pack, 2 x MPI_Sendrecv, unpack — of fortran/mpi+cuda/heat.F90:145-193 entirely. */
+#define HEAT_PEER_BLOB_BYTES 256
+int heat_peer_export(heat_handle* h, void* blob);
+int heat_peer_attach(heat_handle* h, const void* up_blob, const void* down_blob);
+
 /* Synchronise and copy the current field out: this rank's rows, dense [nrows][nx], to `dst`
  * (dst_is_device 0/1).  With global_root >= 0 the call is collective and rank `global_root`
  * receives the whole [ny][nx] field instead (other ranks pass dst = NULL).

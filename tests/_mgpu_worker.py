@@ -34,13 +34,20 @@ def main():
         (512, 1000, 40, 8, True, 4, "tma", np.float64),
         (512, 1000, 37, 8, True, 2, "tma", np.float32),
         (1024, 2048, 30, 16, True, 1, "tma", np.float64),
+        # peer-memory halo (CUDA IPC + copy engines + flag words) instead of NCCL
+        (64, 96, 9, 1, False, 1, "simple", np.float64, True),
+        (203, 130, 23, 4, True, 2, "tma", np.float64, True),
+        (1024, 2048, 33, 16, True, 1, "tma", np.float64, True),
+        (512, 1000, 37, 8, True, 4, "wtma", np.float32, True),
     ]
-    for ci, (ny, nx, steps, g, overlap, k, kernel, dtype) in enumerate(cases):
+    for ci, case in enumerate(cases):
+        ny, nx, steps, g, overlap, k, kernel, dtype = case[:8]
+        peer = len(case) > 8 and case[8]
         full = (1.0 + np.random.default_rng(100 + ci).random((ny, nx))).astype(dtype)
         r0, nr = hd.my_rows(ny)
         nccl_id = hd.shared_nccl_id()              # a ncclUniqueId serves exactly one communicator
         s = hd.slab_solver(full[r0:r0 + nr], ny, R100, 0.2437, nccl_id=nccl_id, device=local, order="pyserial",
-                           kernel=kernel, tblock=k, ghost=g, overlap=overlap)
+                           kernel=kernel, tblock=k, ghost=g, overlap=overlap, peer_halo=peer)
         s.step(steps // 2)
         s.step(steps - steps // 2)                 # split: exercises ghost state carried between calls
         got = s.gather(root=0)
@@ -65,7 +72,7 @@ def main():
                                  float(want.astype(np.float64).sum()),
                                  "one!=want at %s" % np.argwhere(one != want)[:6].tolist(),
                                  "local!=want at %s" % np.argwhere(local_rows != want[r0:r0 + nr])[:6].tolist()))
-            print("case %d %s exchanges=%d launches=%d" % (ci, "ok" if ok else "FAIL", t.halo_exchanges, t.kernel_launches), flush=True)
+            print("case %d%s %s exchanges=%d launches=%d" % (ci, " (peer)" if peer else "", "ok" if ok else "FAIL", t.halo_exchanges, t.kernel_launches), flush=True)
     flag = torch.tensor([len(failures)], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()
