@@ -217,9 +217,19 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     int seg = 0;
     if (const char* v = getenv("HEAT_TEMPORAL_SEG")) seg = atoi(v);
     if (seg <= 0) {
-        const int target = sm_count * 12 * 3;                 // ~3 waves of 12 resident warps per SM
-        const int nseg = std::max(1, target / nstrips);
-        seg = std::max(64 * K, (rows + nseg - 1) / nseg);
+        // Work items are warps; about 12 are resident per SM (3 CTAs, shared-memory bound).  Prefer a whole
+        // number of waves (3, 2 or 1) with segments long enough that the 2K re-read rows stay cheap; a grid
+        // too small for that gets exactly one wave, whatever the segment length.
+        const int resident = sm_count * 12;
+        for (int w = 3; w >= 1 && seg <= 0; --w) {
+            const int nseg = std::max(1, w * resident / nstrips);
+            const int cand = (rows + nseg - 1) / nseg;
+            if (cand >= 48 * K) seg = cand;
+        }
+        if (seg <= 0) {
+            const int nseg = std::max(1, resident / nstrips);
+            seg = std::max(8 * K, (rows + nseg - 1) / nseg);
+        }
     }
     seg = std::min(seg, rows);
     const int nsegs = (rows + seg - 1) / seg;

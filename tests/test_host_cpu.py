@@ -125,3 +125,29 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b|liboracle|oracle/", src, re.M), f
+
+
+def test_serial_save_field_is_the_reference_dump_format(tmp_path):
+    """serial.save_field writes `x y u` lines, x (contiguous index) outer — what fortran/serial/out.py parses."""
+    from heatb200 import serial
+    serial.configure(n=9)
+    serial.u[:] = np.arange(81, dtype=float).reshape(9, 9) / 7.0
+    p = tmp_path / "soln.dat"
+    serial.save_field(str(p))
+    X, Y, Z = ho.read_soln(str(p))
+    assert np.array_equal(Z, serial.u.T) and np.array_equal(X[:, 0], serial.x) and np.array_equal(Y[0], serial.y)
+    serial.configure(n=31)
+
+
+def test_dropins_configure_from_input_deck(tmp_path):
+    from heatb200 import serial, cuda
+    p = tmp_path / "input.dat"
+    p.write_text("100 0.25 0.05 2.0 1000\n")
+    serial.configure(str(p))
+    assert (serial.nx, serial.ny, serial.nt) == (100, 100, 1000) and serial.u.shape == (100, 100)
+    assert serial.dx == 2.0 / 99
+    cuda.configure(str(p))
+    assert (cuda.nx, cuda.nt) == (100, 999) and cuda.u_new.shape == (100, 100)   # nt + 1 launches = ntime
+    assert cuda.r == (cuda.nu * cuda.dt) / cuda.dx**2
+    serial.configure(n=31)
+    cuda.configure(n=4096, nt_=10000)
