@@ -213,9 +213,19 @@ inline int tma_make_map(CUtensorMap* map, void* base, bool f32, long pitch, int 
     cuuint64_t strides[1] = {(cuuint64_t)pitch * es};
     cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)box_h};
     cuuint32_t estr[2] = {1, 1};
+    // L2 promotion: measured (profiles/README.md) — 256 B helps fields of about L2 size (4096^2), 64 B is best
+    // once the field is many times larger than the 126 MB L2 (16384^2: 388.7 vs 380.7 GLUPS)
+    const size_t field_bytes = (size_t)pitch * rows * es;
+    CUtensorMapL2promotion promo = field_bytes > (size_t)512 << 20 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                                                   : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+    if (const char* v = getenv("HEAT_TMA_L2PROMO")) {          // tuning knob: 0 none, 1 64 B, 2 128 B, 3 256 B
+        const int k = atoi(v);
+        promo = k == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : k == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+              : k == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+    }
     CUresult r = enc(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims,
                      strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         err = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r);
         return -2;

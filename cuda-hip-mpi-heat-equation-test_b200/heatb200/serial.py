@@ -80,10 +80,8 @@ def diffuse(nt):
 def save_field(path="soln.dat"):
     """`x y u` per line, contiguous (x) index outer — the Fortran programs' dump format
     (fortran/serial/heat.f90:77-83), readable by the reference's out.py."""
-    with open(path, "w") as f:
-        for i in range(nx):
-            for j in range(ny):
-                f.write("  %-25.17g  %-25.17g  %-25.17g\n" % (x[i], y[j], u[j, i]))
+    from . import io as _io
+    _io.write_dump(path, x, y, u)
 
 
 def main(argv=None):

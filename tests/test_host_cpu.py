@@ -151,3 +151,30 @@ def test_dropins_configure_from_input_deck(tmp_path):
     assert cuda.r == (cuda.nu * cuda.dt) / cuda.dx**2
     serial.configure(n=31)
     cuda.configure(n=4096, nt_=10000)
+
+
+def test_io_dump_roundtrip_and_rank_files(tmp_path):
+    from heatb200 import io as hio
+    n = 14
+    delta = ho.derive_fortran(n, 0.25, 0.05, 2.0)[0]
+    c = ic.fortran_coords(n, 2.0, delta)
+    T = ho.fortran_serial(n, 0.25, 0.05, 2.0, 4)
+    p = str(tmp_path / "soln.dat")
+    hio.write_dump(p, c, c, T)
+    x, y, T2 = hio.read_dump(p)
+    assert np.array_equal(x, c) and np.array_equal(y, c) and np.array_equal(T2, T)
+    X, Y, Z = ho.read_soln(p)                       # the oracle's reader (out.py's logic) agrees
+    assert np.array_equal(Z, T.T)
+    # the oracle's writer and ours produce the same numbers
+    q = str(tmp_path / "soln_oracle.dat")
+    ho.write_soln(q, c, c, T)
+    assert np.array_equal(np.loadtxt(q), np.loadtxt(p))
+    # per-rank files tile the field
+    parts = []
+    for r in range(3):
+        r0, nr = heatb200.slab_partition(n, 3, r)
+        f = hio.write_rank_dump(str(tmp_path), r, c, c[r0:r0 + nr], T[r0:r0 + nr])
+        assert f.endswith("soln%05d.dat" % r)
+        parts.append(hio.read_dump(f)[2])
+    assert np.array_equal(np.concatenate(parts), T)
+    assert abs(hio.checksum_host(T) - T.sum()) < 1e-9
