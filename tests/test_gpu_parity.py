@@ -212,6 +212,32 @@ def test_cuda_dropin_small():
     assert (cuda.run() == 1.0).all()
 
 
+def test_cuda_dropin_reference_size_and_step_count():
+    """python/cuda/cuda.py as shipped: 4096^2, nt = 10000 -> 10001 launches; its (empty-slice) field is the
+    fixed point 1.  With the intended hat the 10001-step result must not depend on how steps are fused."""
+    from heatb200 import cuda
+    cuda.configure(n=4096, nt_=10000)
+    out = cuda.run()
+    assert out.shape == (4096, 4096) and (out == 1.0).all()
+    cuda.configure(n=4096, nt_=10000, hat=True)
+    u0 = cuda.u_new.copy()
+    a = cuda.run()
+    b = heatb200.march(u0, 10001, cuda.r, order="pycuda", kernel="tma", tblock=4)
+    assert_bit_equal(a, b)
+    assert 1.0 <= a.min() and a.max() < 2.0                      # maximum principle after 10001 steps
+    assert np.abs(a - a.T).max() < 1e-11                         # symmetric up to rounding (W+E is summed before N+S)
+
+
+def test_many_back_to_back_launches_small_grid():
+    """2000 dependent launches of a grid far smaller than the GPU (programmatic dependent launch lets the
+    next step's CTAs start early): any ordering bug shows up against the one-launch RESIDENT kernel."""
+    u0 = rand_field((96, 160), seed=21)
+    want = heatb200.march(u0, 2000, R100, kernel="resident")
+    assert_bit_equal(want, c_oracle.march(u0, 2000, 0, R100))
+    for kernel, k in [("tma", 1), ("wtma", 1), ("tma", 2), ("tma", 4), ("stream", 1)]:
+        assert_bit_equal(heatb200.march(u0, 2000, R100, kernel=kernel, tblock=k), want)
+
+
 # ------------------------------------------------------------------ full-size properties (BASELINE sizes)
 def test_4096_kernels_agree_and_match_c_oracle():
     n = 4096
