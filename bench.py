@@ -195,7 +195,7 @@ def main():
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--tblock", type=int, default=1)
     ap.add_argument("--fmad", action="store_true")
-    ap.add_argument("--ghost", type=int, default=int(os.environ.get("HEAT_BENCH_GHOST", "16")))
+    ap.add_argument("--ghost", type=int, default=int(os.environ.get("HEAT_BENCH_GHOST", "32")))
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--skip-exchange", action="store_true", help="diagnostic: no halo traffic (results wrong)")
     ap.add_argument("--peer-halo", action="store_true", help="halo rows by CUDA-IPC peer copies instead of NCCL")
