@@ -304,10 +304,10 @@ def main():
     launches = tm.kernel_launches - l0
     value = lups_per_step * args.steps / (ms * 1e-3) / 1e9
 
-    # ---- roofline of the dominant kernel: algorithmic bytes per launch / average launch duration.
-    # last_step_ms is the CUDA-event time of the last heat_step on the stream its kernels run on.
+    # ---- roofline of the dominant kernel: algorithmic bytes per launch / average launch duration over the
+    # timed region (CUDA events on the stream the kernels are launched on; launch gaps are charged to the kernel)
     launches_per_step = launches / args.steps
-    avg_kernel_ms = tm.last_step_ms / max(launches_per_step, 1)
+    avg_kernel_ms = ms / max(launches, 1)
     local_lups_per_launch = (nx - 2) * (min(row0 + nrows, ny_global - 1) - max(row0, 1)) * timesteps / max(launches_per_step, 1)
     # algorithmic DRAM bytes per lattice update: read + write once per HBM round trip of `tblock` fused steps
     bytes_per_lup = 2 * esize / max(args.tblock, 1)

@@ -92,6 +92,7 @@ struct heat_handle {
     int sm_count = 148;
     int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
     uint64_t steps_total = 0, launches = 0, exchanges = 0;
+    int kflags = 0;                // KF_* of the next launches: sweep direction (alternates per advance) + L2 policy
 };
 
 static const int kSumBlocks = 592;   // 148 SMs x 4; fixed so the checksum's reduction tree is fixed
@@ -131,10 +132,10 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
     } else if (h->kernel == HEAT_KERNEL_WTMA) {
         const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;
         return launch_temporal_rows<T, ORDER, FMA, 1>(h->temporal, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch, yb, ye,
-                                                     ybc0, ybc1, rx, ry, h->sm_count, s);
+                                                     ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
     } else if (h->kernel == HEAT_KERNEL_TMA) {
         return launch_tma_rows<T, ORDER, FMA>(h->tma, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch,
-                                              yb, ye, rx, ry, h->sm_count, s);
+                                              yb, ye, rx, ry, h->sm_count, s, h->kflags);
     } else {
         dim3 block(32, 8);
         dim3 grid((h->nx - 2 + 31) / 32, (rows + 7) / 8);
@@ -164,8 +165,8 @@ static cudaError_t launch_fused_t(heat_handle* h, const void* src, void* dst, in
     const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;   // local rows of global rows 0, ny-1
     h->launches++;
     switch (h->tblock) {
-        case 2: return launch_temporal_rows<T, ORDER, FMA, 2>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s);
-        case 4: return launch_temporal_rows<T, ORDER, FMA, 4>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s);
+        case 2: return launch_temporal_rows<T, ORDER, FMA, 2>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
+        case 4: return launch_temporal_rows<T, ORDER, FMA, 4>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
     }
     return cudaErrorInvalidValue;
 }
@@ -463,6 +464,7 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     h->esize = cfg->dtype == HEAT_F32 ? 4 : 8;
     h->fma = (cfg->flags & HEAT_FLAG_FMAD) != 0;
     h->tblock = cfg->tblock > 0 ? cfg->tblock : 1;
+    h->kflags = sweep_policy_flags();
     h->stream_rows = env_int("HEAT_STREAM_ROWS", 0);
     h->stream_threads = env_int("HEAT_STREAM_THREADS", 0);
     int rc = heat_slab_partition(h->ny, cfg->nranks, cfg->rank, &h->row0, &h->nrows);
@@ -651,10 +653,12 @@ int heat_step(heat_handle* h, int nt) {
             for (; h->tblock > 1 && t + h->tblock <= nt; t += h->tblock) {
                 CUDA_TRY(update_rows_fused(h, 1, h->ny - 2, h->s_compute));
                 h->cur ^= 1;
+                if (serpentine_enabled()) h->kflags ^= KF_REVERSE;
             }
             for (; t < nt; ++t) {
                 CUDA_TRY(update_rows(h, 1, h->ny - 2, h->s_compute));
                 h->cur ^= 1;
+                if (serpentine_enabled()) h->kflags ^= KF_REVERSE;
             }
         } else {
             const bool overlap = (h->cfg.flags & HEAT_FLAG_OVERLAP) && h->nrows >= 2 * h->g;
@@ -697,6 +701,7 @@ int heat_step(heat_handle* h, int nt) {
                     }
                 }
                 h->cur ^= 1;
+                if (serpentine_enabled()) h->kflags ^= KF_REVERSE;
                 t += adv;
             }
             int rc = wait_comm(h);   // the timed region of this call ends after its last exchange

@@ -37,7 +37,7 @@ template <typename T, int ORDER, bool FMA, int K, int M>
 __global__ void __launch_bounds__(kTempWarps * 32)
 heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
                      int y_begin, int y_end, int seg_rows, int nstrips, int nitems, int ybc0, int ybc1,
-                     T rx, T ry, int pdl_early) {
+                     T rx, T ry, int pdl_early, int kflags) {
     constexpr int V = Pack<T>::V;
     using P = Pack<T>;
     constexpr int MV = M * V;                     // cells per lane
@@ -51,9 +51,12 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int item = blockIdx.x * kTempWarps + warp;
+    const int item_fwd = blockIdx.x * kTempWarps + warp;
     if (pdl_early) pdl_launch_dependents();
-    if (item >= nitems) return;                   // whole warps leave; nothing below syncs across warps
+    if (item_fwd >= nitems) return;               // whole warps leave; nothing below syncs across warps
+    const int item = (kflags & KF_REVERSE) ? nitems - 1 - item_fwd : item_fwd;
+    const bool ld_hint = kflags & KF_LOAD_EVICT_FIRST, st_hinted = kflags & KF_STORE_EVICT_LAST;
+    const uint64_t pol_ld = policy_evict_first(), pol_st = policy_evict_last();
     const int strip = item % nstrips, seg = item / nstrips;
     const int xs = strip * WOUT - HX;             // first column of the loaded strip
     const int ys = y_begin + seg * seg_rows;
@@ -67,7 +70,8 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
     auto issue = [&](int j) {
         const int slot = j % S;
         mbar_expect_tx(&full[slot], kStageBytes);
-        tma_load_2d(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot]);
+        if (ld_hint) tma_load_2d_hint(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot], pol_ld);
+        else tma_load_2d(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot]);
     };
     if (lane == 0) {
 #pragma unroll
@@ -157,7 +161,8 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
                         P out;
 #pragma unroll
                         for (int i = 0; i < V; ++i) out.v[i] = outrow[m * V + i];
-                        *reinterpret_cast<P*>(orow + m * V) = out;
+                        if (st_hinted) st_hint(orow + m * V, out, pol_st);
+                        else *reinterpret_cast<P*>(orow + m * V) = out;
                     }
                 }
             }
@@ -203,7 +208,7 @@ inline int temporal_setup(TemporalState& st, void* const buf[2], bool f32, int r
 
 template <typename T, int ORDER, bool FMA, int K>
 inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* dst, int nx, long pitch, int yb,
-                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s) {
+                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags) {
     constexpr int V = Pack<T>::V;
     constexpr int M = 2;
     constexpr int WIN = 32 * M * V, HX = TemporalGeom<T, K>::HX, WOUT = WIN - 2 * HX;
@@ -238,8 +243,8 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     // signal dependents at CTA start only when the grid spans several waves: early-placed CTAs of the next
     // launch would otherwise skew the balance of a grid that does not even fill the machine once
     const int pdl_early = grid >= 2 * sm_count * 4 ? 1 : 0;
-    return launch_pdl(k, dim3(grid), dim3(kTempWarps * 32), smem, s, st.map[which], dst, nx, pitch, yb, ye, seg,
-                      nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early);
+    return launch_pdl(k, dim3(grid), dim3(kTempWarps * 32), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg,
+                      nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early, kflags);
 }
 
 }  // namespace heat

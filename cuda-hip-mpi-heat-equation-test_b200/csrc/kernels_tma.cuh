@@ -15,6 +15,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <string>
 
 #include "stencil_ops.cuh"
@@ -71,25 +72,117 @@ inline bool pdl_enabled() {
     return on;
 }
 
+// L2 residency experiment (OFF unless HEAT_L2_PERSIST_MB is set): pin the bytes a step writes last — the
+// bytes the next, opposite-direction step reads first — in the persisting part of L2 with a per-launch
+// access-policy window.  Measured on B200 it LOSES (4096^2: 407 -> 335-401 GLUPS for 32-128 MB windows;
+// 16384^2: 385 -> 227): the carve-out costs more ordinary L2 capacity than the pinned lines give back.
+// Plain serpentine sweeping (below) keeps the gain without it.
+struct L2Window {
+    void* base = nullptr;
+    size_t bytes = 0;
+};
+
+inline size_t l2_persist_bytes() {       // how much L2 this process may pin (set up once per process/device)
+    static const size_t n = [] {
+        int dev = 0, max_persist = 0, max_window = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+        const char* v = getenv("HEAT_L2_PERSIST_MB");
+        if (!v) return (size_t)0;
+        const size_t want = std::min((size_t)std::min(max_persist, max_window), (size_t)atol(v) << 20);
+        if (want == 0) return (size_t)0;
+        if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) { cudaGetLastError(); return (size_t)0; }
+        return want;
+    }();
+    return n;
+}
+
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, L2Window win,
+                              Args... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    if (win.base && win.bytes) {
+        attr[1].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[1].val.accessPolicyWindow.base_ptr = win.base;
+        attr[1].val.accessPolicyWindow.num_bytes = win.bytes;
+        attr[1].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[1].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[1].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.numAttrs = 2;
+    }
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+// the tail of a sweep over rows [yb, ye) of `dst`: its last rows when sweeping forward, its first when reversed
+template <typename T>
+inline L2Window sweep_tail_window(T* dst, long pitch, int yb, int ye, int kflags) {
+    L2Window w;
+    const size_t cap = l2_persist_bytes();
+    if (cap == 0) return w;
+    const size_t row = (size_t)pitch * sizeof(T);
+    const size_t span = (size_t)(ye - yb) * row;
+    w.bytes = std::min(cap, span);
+    w.base = (kflags & 1) ? (char*)dst + (size_t)yb * row : (char*)dst + (size_t)ye * row - w.bytes;
+    return w;
+}
+
+// L2 cache-policy variants (tuning knobs; measured in profiles/README.md).  The field is swept in opposite
+// directions on alternate steps (serpentine), so the rows written last — still in the 126 MB L2 — are the
+// rows read first by the next step.
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const CUtensorMap* map, int cx, int cy, uint64_t* bar,
+                                                 uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(cx), "r"(cy), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void st_hint(double* p, const Pack<double>& v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(v.v[0]), "d"(v.v[1]), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void st_hint(float* p, const Pack<float>& v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.v[0]), "f"(v.v[1]),
+                 "f"(v.v[2]), "f"(v.v[3]), "l"(policy) : "memory");
+}
+
+// kflags: bit 0 = sweep the grid in reverse block order; bit 1 = evict-first loads; bit 2 = evict-last stores
+enum : int { KF_REVERSE = 1, KF_LOAD_EVICT_FIRST = 2, KF_STORE_EVICT_LAST = 4 };
+
+inline int sweep_policy_flags() {
+    static const int f = [] {
+        const char* v = getenv("HEAT_CACHE_HINT");       // tuning knob: 0 none, 1 loads, 2 loads+stores, 3 stores
+        const int m = v ? atoi(v) : 0;
+        return (m == 1 || m == 2 ? KF_LOAD_EVICT_FIRST : 0) | (m == 2 || m == 3 ? KF_STORE_EVICT_LAST : 0);
+    }();
+    return f;
+}
+inline bool serpentine_enabled() {
+    static const bool on = [] { const char* v = getenv("HEAT_SERPENTINE"); return !(v && v[0] == '0'); }();
+    return on;
 }
 
 template <typename T, int ORDER, bool FMA>
 __global__ void __launch_bounds__(kTmaThreads)
 heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
-                int y_begin, int y_end, int seg_rows, T rx, T ry) {
+                int y_begin, int y_end, int seg_rows, T rx, T ry, int kflags) {
     constexpr int V = Pack<T>::V;
     using P = Pack<T>;
     constexpr int BX = kTmaBX, BY = kTmaBY, S = kTmaStages;
@@ -108,10 +201,15 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int col = tid % LPR, sub = tid / LPR;
-    const int x0 = blockIdx.x * BX;
-    const int ys = y_begin + blockIdx.y * seg_rows;
+    const bool rev = kflags & KF_REVERSE;
+    const int bx = rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+    const int by = rev ? gridDim.y - 1 - blockIdx.y : blockIdx.y;
+    const int x0 = bx * BX;
+    const int ys = y_begin + by * seg_rows;
     const int ye = min(ys + seg_rows, y_end);
     if (ys >= ye) return;
+    const bool ld_hint = kflags & KF_LOAD_EVICT_FIRST, st_hinted = kflags & KF_STORE_EVICT_LAST;
+    const uint64_t pol_ld = policy_evict_first(), pol_st = policy_evict_last();
     const int np = ye - ys;                         // centres p = 1..np  (global row ys-1+p)
     const int nstages = (np + 2 + BY - 1) / BY;     // input rows p = 0..np+1
 
@@ -127,7 +225,8 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
     auto issue = [&](int j) {
         const int slot = j % S;
         mbar_expect_tx(&full[slot], kStageBytes);
-        tma_load_2d(ring + (size_t)slot * BY * BW, &tmap, x0 - V, ys - 1 + j * BY, &full[slot]);
+        if (ld_hint) tma_load_2d_hint(ring + (size_t)slot * BY * BW, &tmap, x0 - V, ys - 1 + j * BY, &full[slot], pol_ld);
+        else tma_load_2d(ring + (size_t)slot * BY * BW, &tmap, x0 - V, ys - 1 + j * BY, &full[slot]);
     };
     if (tid == 0) {
         for (int j = 0; j < S - 1 && j < nstages; ++j) issue(j);
@@ -177,8 +276,11 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
                 const long x = xg + v;
                 o.v[v] = (x >= 1 && x <= nx - 2) ? r : c.v[v];
             }
-            if (active && p >= 1 && p <= np)
-                *reinterpret_cast<P*>(dst + (long)(ys - 1 + p) * pitch + xg) = o;
+            if (active && p >= 1 && p <= np) {
+                T* q = dst + (long)(ys - 1 + p) * pitch + xg;
+                if (st_hinted) st_hint(q, o, pol_st);
+                else *reinterpret_cast<P*>(q) = o;
+            }
         }
         __syncthreads();                            // everyone is done with stage j-1 (and j's reads)
         if (tid == 0 && j + S - 1 < nstages) issue(j + S - 1);
@@ -248,7 +350,7 @@ inline int tma_setup(TmaState& st, void* const buf[2], bool f32, int nx, int row
 
 template <typename T, int ORDER, bool FMA>
 inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx, long pitch, int yb, int ye,
-                                   T rx, T ry, int sm_count, cudaStream_t s) {
+                                   T rx, T ry, int sm_count, cudaStream_t s, int kflags) {
     constexpr int V = Pack<T>::V;
     constexpr size_t smem = (size_t)kTmaStages * kTmaBY * (kTmaBX + 2 * V) * sizeof(T) + kTmaStages * sizeof(uint64_t);
     auto k = heat_tma_kernel<T, ORDER, FMA>;
@@ -266,7 +368,7 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     }
     seg = std::min(seg, rows);
     const int gy = (rows + seg - 1) / seg;
-    return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry);
+    return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry, kflags);
 }
 
 }  // namespace heat
