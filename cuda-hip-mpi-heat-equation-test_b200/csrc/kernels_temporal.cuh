@@ -215,7 +215,7 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     constexpr size_t smem = (size_t)kTempWarps * kTempStages * kTempRS * WIN * sizeof(T) +
                             (size_t)kTempWarps * kTempStages * sizeof(uint64_t);
     auto k = heat_temporal_kernel<T, ORDER, FMA, K, M>;
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = ensure_dynamic_smem<heat_temporal_kernel<T, ORDER, FMA, K, M>>(smem);
     if (e != cudaSuccess) return e;
     const int rows = ye - yb;
     const int nstrips = (int)((pitch + WOUT - 1) / WOUT);

@@ -123,6 +123,21 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per kernel instantiation and device, not per launch
+// (keyed by the kernel itself — a non-type template argument — because instantiations that differ only in
+// ORDER/FMA share one function-pointer type)
+template <auto Kernel>
+inline cudaError_t ensure_dynamic_smem(size_t smem) {
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
+    e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
+    return e;
+}
+
 // the tail of a sweep over rows [yb, ye) of `dst`: its last rows when sweeping forward, its first when reversed
 template <typename T>
 inline L2Window sweep_tail_window(T* dst, long pitch, int yb, int ye, int kflags) {
@@ -354,7 +369,7 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     constexpr int V = Pack<T>::V;
     constexpr size_t smem = (size_t)kTmaStages * kTmaBY * (kTmaBX + 2 * V) * sizeof(T) + kTmaStages * sizeof(uint64_t);
     auto k = heat_tma_kernel<T, ORDER, FMA>;
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = ensure_dynamic_smem<heat_tma_kernel<T, ORDER, FMA>>(smem);
     if (e != cudaSuccess) return e;
     const int rows = ye - yb;
     const int gx = (int)((pitch + kTmaBX - 1) / kTmaBX);
