@@ -198,7 +198,9 @@ def main():
     ap.add_argument("--ghost", type=int, default=int(os.environ.get("HEAT_BENCH_GHOST", "32")))
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--skip-exchange", action="store_true", help="diagnostic: no halo traffic (results wrong)")
-    ap.add_argument("--peer-halo", action="store_true", help="halo rows by CUDA-IPC peer copies instead of NCCL")
+    ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"],
+                    help="halo exchange: peer stores from the edge-strip kernels over CUDA IPC (auto falls back to NCCL "
+                         "if IPC is unavailable) or ncclSend/ncclRecv")
     ap.add_argument("--timesteps", type=int, default=0, help="override time steps per bench step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -268,9 +270,12 @@ def main():
     common = dict(order="fortran", kernel=args.kernel, tblock=args.tblock, fmad=args.fmad, device=local, stream=stream)
     if world > 1:
         solver = hdist.slab_solver(host_in, ny_global, r, nccl_id=nccl_id, ghost=args.ghost, overlap=not args.no_overlap,
-                                   skip_exchange=args.skip_exchange, peer_halo=args.peer_halo, **common)
+                                   skip_exchange=args.skip_exchange,
+                                   peer_halo={"auto": "auto", "peer": True, "nccl": False}[args.halo], **common)
     else:
         solver = heatb200.HeatSolver(host_in, r, **common)
+    class solver_halo_mode:                                    # remembered for the JSON line (solver is closed by then)
+        v = getattr(solver, "halo_mode", "none")
     lups_per_step = (nx - 2) * (ny_global - 2) * timesteps      # whole job, all ranks
 
     def barrier():
@@ -354,7 +359,7 @@ def main():
             "config": {"workload": args.workload + ": " + wl["desc"], "nx": nx, "ny_global": ny_global,
                        "timesteps_per_step": timesteps, "kernel": roofline["kernel"], "tblock": args.tblock,
                        "fmad": bool(args.fmad), "op_order": "fortran",
-                       "parallelism": "row-slabs x%d" % world + (", ghost %d, overlap %s, halo via %s" % (args.ghost, not args.no_overlap, "peer copies (CUDA IPC)" if args.peer_halo else "NCCL send/recv") if world > 1 else ""),
+                       "parallelism": "row-slabs x%d" % world + (", ghost %d, overlap %s, halo via %s" % (args.ghost, not args.no_overlap, solver_halo_mode.v) if world > 1 else ""),
                        "l2": "working set %.0f MB per GPU vs 126 MB L2: inputs larger than L2, no flush" % (2 * nrows * nx * esize / 1e6)},
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(total_launches),
             "clocks": clk.summary(),

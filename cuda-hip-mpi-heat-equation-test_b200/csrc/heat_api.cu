@@ -92,6 +92,8 @@ struct heat_handle {
     int sm_count = 148;
     int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
     uint64_t steps_total = 0, launches = 0, exchanges = 0;
+    void* mirror_base = nullptr;   // transient: second destination (peer ghost rows) of the next update launch
+    int mirror_shift = 0;
     int kflags = 0;                // KF_* of the next launches: sweep direction (alternates per advance) + L2 policy
 };
 
@@ -132,10 +134,10 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
     } else if (h->kernel == HEAT_KERNEL_WTMA) {
         const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;
         return launch_temporal_rows<T, ORDER, FMA, 1>(h->temporal, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch, yb, ye,
-                                                     ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
+                                                     ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
     } else if (h->kernel == HEAT_KERNEL_TMA) {
         return launch_tma_rows<T, ORDER, FMA>(h->tma, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch,
-                                              yb, ye, rx, ry, h->sm_count, s, h->kflags);
+                                              yb, ye, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
     } else {
         dim3 block(32, 8);
         dim3 grid((h->nx - 2 + 31) / 32, (rows + 7) / 8);
@@ -165,8 +167,8 @@ static cudaError_t launch_fused_t(heat_handle* h, const void* src, void* dst, in
     const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;   // local rows of global rows 0, ny-1
     h->launches++;
     switch (h->tblock) {
-        case 2: return launch_temporal_rows<T, ORDER, FMA, 2>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
-        case 4: return launch_temporal_rows<T, ORDER, FMA, 4>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags);
+        case 2: return launch_temporal_rows<T, ORDER, FMA, 2>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
+        case 4: return launch_temporal_rows<T, ORDER, FMA, 4>(h->temporal, which, (T*)dst, h->nx, h->pitch, yb, ye, ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
     }
     return cudaErrorInvalidValue;
 }
@@ -244,34 +246,37 @@ static PFN_streamWaitValue32 get_wait_value32() {
     return fn;
 }
 
-static int exchange_peer(heat_handle* h, int which, cudaStream_t s) {
+// phase 0: "ready" flags, phase 1: "done" flags.  Signal the neighbours, then block the stream until both have signalled us.
+static int peer_handshake(heat_handle* h, int phase, uint32_t epoch, cudaStream_t s) {
     PFN_streamWaitValue32 wait32 = get_wait_value32();
     if (!wait32) return fail(HEAT_ERR_UNSUPPORTED, "peer halo: cuStreamWaitValue32 is not available from this driver");
+    const bool up = h->cfg.rank > 0, down = h->cfg.rank + 1 < h->cfg.nranks;
+    // I am the up neighbour's "down" and the down neighbour's "up"
+    heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 2 * phase + 1 : nullptr, down ? h->down_flags + 2 * phase : nullptr, epoch);
+    CUDA_TRY(cudaGetLastError());
+    for (int side = 0; side < 2; ++side) {
+        if (!(side == 0 ? up : down)) continue;
+        CUresult r = wait32((CUstream)s, (CUdeviceptr)(uintptr_t)(h->d_flags + 2 * phase + side), epoch, CU_STREAM_WAIT_VALUE_GEQ);
+        if (r != CUDA_SUCCESS) return fail(HEAT_ERR_CUDA, "cuStreamWaitValue32 failed with CUresult %d", (int)r);
+    }
+    return HEAT_OK;
+}
+
+static int exchange_peer(heat_handle* h, int which, cudaStream_t s) {
     const uint32_t epoch = ++h->epoch;
     const bool up = h->cfg.rank > 0, down = h->cfg.rank + 1 < h->cfg.nranks;
     const size_t bytes = (size_t)h->g * row_bytes(h);
-    auto wait_flag = [&](int idx) -> int {
-        CUresult r = wait32((CUstream)s, (CUdeviceptr)(uintptr_t)(h->d_flags + idx), epoch, CU_STREAM_WAIT_VALUE_GEQ);
-        if (r != CUDA_SUCCESS) return fail(HEAT_ERR_CUDA, "cuStreamWaitValue32 failed with CUresult %d", (int)r);
-        return HEAT_OK;
-    };
     CUDA_TRY(cudaEventRecord(h->ev_h0, s));
-    // I am the up neighbour's "down" and the down neighbour's "up"
-    heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 1 : nullptr, down ? h->down_flags + 0 : nullptr, epoch);
-    CUDA_TRY(cudaGetLastError());
-    int rc;
-    if (up && (rc = wait_flag(0))) return rc;
-    if (down && (rc = wait_flag(1))) return rc;
+    int rc = peer_handshake(h, 0, epoch, s);
+    if (rc) return rc;
     if (up)     // my first g rows -> the bottom ghost rows of the rank above
         CUDA_TRY(cudaMemcpyAsync((char*)h->up_buf[which] + (size_t)(h->g + h->up_nrows) * row_bytes(h),
                                  row_ptr(h, which, h->g), bytes, cudaMemcpyDeviceToDevice, s));
     if (down)   // my last g rows -> the top ghost rows of the rank below
         CUDA_TRY(cudaMemcpyAsync((char*)h->down_buf[which], row_ptr(h, which, h->nrows), bytes,
                                  cudaMemcpyDeviceToDevice, s));
-    heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 3 : nullptr, down ? h->down_flags + 2 : nullptr, epoch);
-    CUDA_TRY(cudaGetLastError());
-    if (up && (rc = wait_flag(2))) return rc;
-    if (down && (rc = wait_flag(3))) return rc;
+    rc = peer_handshake(h, 1, epoch, s);
+    if (rc) return rc;
     CUDA_TRY(cudaEventRecord(h->ev_h1, s));
     h->halo_timed = true;
     return HEAT_OK;
@@ -617,12 +622,10 @@ int heat_peer_attach(heat_handle* h, const void* up_blob, const void* down_blob)
     if (up && (rc = open_one(up_blob, h->cfg.rank - 1, h->up_buf, &h->up_flags, &h->up_nrows))) return rc;
     if (down && (rc = open_one(down_blob, h->cfg.rank + 1, h->down_buf, &h->down_flags, nullptr))) return rc;
     h->peer_ready = true;
-    // first ghost fill (collective): both buffers, as heat_set_field does on the NCCL path
-    for (int b = 0; b < 2; ++b)
-        if ((rc = exchange(h, b, h->s_compute))) return rc;
-    h->valid_ghost = h->g;
+    // No cross-GPU wait happens here, so a rank whose attach failed cannot leave its neighbours blocked: the
+    // ghosts are filled by the first heat_step / heat_halo_exchange (valid_ghost == 0 forces an exchange).
+    h->valid_ghost = 0;
     h->peer_pending_fill = false;
-    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
     return HEAT_OK;
 }
 
@@ -683,10 +686,37 @@ int heat_step(heat_handle* h, int nt) {
                     auto upd_on = [&](int lo, int hi, cudaStream_t st) { return adv > 1 ? update_rows_fused(h, lo, hi, st) : update_rows(h, lo, hi, st); };
                     CUDA_TRY(cudaEventRecord(h->ev_boundary, h->s_compute));
                     CUDA_TRY(cudaStreamWaitEvent(h->s_comm, h->ev_boundary, 0));
-                    CUDA_TRY(upd_on(own_lo, own_lo + h->g - 1, h->s_comm));
-                    CUDA_TRY(upd_on(own_hi - h->g + 1, own_hi, h->s_comm));
-                    rc = exchange(h, h->cur ^ 1, h->s_comm);
-                    if (rc) return rc;
+                    const bool fused_peer = (h->cfg.flags & HEAT_FLAG_PEER_HALO) && h->peer_ready &&
+                                            !(h->cfg.flags & HEAT_FLAG_SKIP_EXCHANGE) &&
+                                            (adv > 1 || h->kernel == HEAT_KERNEL_TMA || h->kernel == HEAT_KERNEL_WTMA);
+                    if (fused_peer) {
+                        // ONE kernel computes an edge strip and pushes it over NVLink: its stores go to the own
+                        // buffer and, as peer stores, to the neighbour's ghost rows.  Handshakes around it:
+                        // "ready" before (the neighbour is done with those ghost rows), "done" after.
+                        const uint32_t epoch = ++h->epoch;
+                        h->exchanges++;
+                        CUDA_TRY(cudaEventRecord(h->ev_h0, h->s_comm));
+                        rc = peer_handshake(h, 0, epoch, h->s_comm);
+                        if (rc) return rc;
+                        const int dstb = h->cur ^ 1;
+                        if (h->cfg.rank > 0) { h->mirror_base = h->up_buf[dstb]; h->mirror_shift = h->up_nrows; }
+                        cudaError_t ce1 = upd_on(own_lo, own_lo + h->g - 1, h->s_comm);
+                        h->mirror_base = nullptr;
+                        CUDA_TRY(ce1);
+                        if (h->cfg.rank + 1 < h->cfg.nranks) { h->mirror_base = h->down_buf[dstb]; h->mirror_shift = -h->nrows; }
+                        cudaError_t ce2 = upd_on(own_hi - h->g + 1, own_hi, h->s_comm);
+                        h->mirror_base = nullptr;
+                        CUDA_TRY(ce2);
+                        rc = peer_handshake(h, 1, epoch, h->s_comm);
+                        if (rc) return rc;
+                        CUDA_TRY(cudaEventRecord(h->ev_h1, h->s_comm));
+                        h->halo_timed = true;
+                    } else {
+                        CUDA_TRY(upd_on(own_lo, own_lo + h->g - 1, h->s_comm));
+                        CUDA_TRY(upd_on(own_hi - h->g + 1, own_hi, h->s_comm));
+                        rc = exchange(h, h->cur ^ 1, h->s_comm);
+                        if (rc) return rc;
+                    }
                     CUDA_TRY(cudaEventRecord(h->ev_comm, h->s_comm));
                     h->comm_pending = true;
                     CUDA_TRY(upd(own_lo + h->g, own_hi - h->g));

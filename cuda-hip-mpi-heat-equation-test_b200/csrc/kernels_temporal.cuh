@@ -37,7 +37,7 @@ template <typename T, int ORDER, bool FMA, int K, int M>
 __global__ void __launch_bounds__(kTempWarps * 32)
 heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
                      int y_begin, int y_end, int seg_rows, int nstrips, int nitems, int ybc0, int ybc1,
-                     T rx, T ry, int pdl_early, int kflags) {
+                     T rx, T ry, int pdl_early, int kflags, T* __restrict__ dst2, int shift2) {
     constexpr int V = Pack<T>::V;
     using P = Pack<T>;
     constexpr int MV = M * V;                     // cells per lane
@@ -163,6 +163,8 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
                         for (int i = 0; i < V; ++i) out.v[i] = outrow[m * V + i];
                         if (st_hinted) st_hint(orow + m * V, out, pol_st);
                         else *reinterpret_cast<P*>(orow + m * V) = out;
+                        if (dst2)   // peer store into the neighbour GPU's ghost row (see kernels_tma.cuh)
+                            *reinterpret_cast<P*>(dst2 + (long)(o + shift2) * pitch + xl + m * V) = out;
                     }
                 }
             }
@@ -208,7 +210,8 @@ inline int temporal_setup(TemporalState& st, void* const buf[2], bool f32, int r
 
 template <typename T, int ORDER, bool FMA, int K>
 inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* dst, int nx, long pitch, int yb,
-                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags) {
+                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags,
+                                        T* dst2 = nullptr, int shift2 = 0) {
     constexpr int V = Pack<T>::V;
     constexpr int M = 2;
     constexpr int WIN = 32 * M * V, HX = TemporalGeom<T, K>::HX, WOUT = WIN - 2 * HX;
@@ -244,7 +247,7 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     // launch would otherwise skew the balance of a grid that does not even fill the machine once
     const int pdl_early = grid >= 2 * sm_count * 4 ? 1 : 0;
     return launch_pdl(k, dim3(grid), dim3(kTempWarps * 32), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg,
-                      nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early, kflags);
+                      nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early, kflags, dst2, shift2);
 }
 
 }  // namespace heat

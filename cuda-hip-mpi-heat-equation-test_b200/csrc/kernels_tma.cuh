@@ -197,7 +197,10 @@ inline bool serpentine_enabled() {
 template <typename T, int ORDER, bool FMA>
 __global__ void __launch_bounds__(kTmaThreads)
 heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
-                int y_begin, int y_end, int seg_rows, T rx, T ry, int kflags) {
+                int y_begin, int y_end, int seg_rows, T rx, T ry, int kflags, T* __restrict__ dst2, int shift2) {
+    // dst2 (optional): the same rows are ALSO stored, shifted by shift2 rows, into a second buffer — the ghost
+    // rows of the neighbouring GPU, mapped through CUDA IPC — so an edge strip's results cross NVLink from
+    // inside the stencil kernel, as peer stores issued next to the local ones (fused compute + halo push).
     constexpr int V = Pack<T>::V;
     using P = Pack<T>;
     constexpr int BX = kTmaBX, BY = kTmaBY, S = kTmaStages;
@@ -295,6 +298,7 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
                 T* q = dst + (long)(ys - 1 + p) * pitch + xg;
                 if (st_hinted) st_hint(q, o, pol_st);
                 else *reinterpret_cast<P*>(q) = o;
+                if (dst2) *reinterpret_cast<P*>(dst2 + (long)(ys - 1 + p + shift2) * pitch + xg) = o;
             }
         }
         __syncthreads();                            // everyone is done with stage j-1 (and j's reads)
@@ -365,7 +369,8 @@ inline int tma_setup(TmaState& st, void* const buf[2], bool f32, int nx, int row
 
 template <typename T, int ORDER, bool FMA>
 inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx, long pitch, int yb, int ye,
-                                   T rx, T ry, int sm_count, cudaStream_t s, int kflags) {
+                                   T rx, T ry, int sm_count, cudaStream_t s, int kflags, T* dst2 = nullptr,
+                                   int shift2 = 0) {
     constexpr int V = Pack<T>::V;
     constexpr size_t smem = (size_t)kTmaStages * kTmaBY * (kTmaBX + 2 * V) * sizeof(T) + kTmaStages * sizeof(uint64_t);
     auto k = heat_tma_kernel<T, ORDER, FMA>;
@@ -383,7 +388,7 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     }
     seg = std::min(seg, rows);
     const int gy = (rows + seg - 1) / seg;
-    return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry, kflags);
+    return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry, kflags, dst2, shift2);
 }
 
 }  // namespace heat

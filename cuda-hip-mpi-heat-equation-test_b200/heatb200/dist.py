@@ -56,11 +56,40 @@ def slab_solver(field_slab: np.ndarray, ny_global: int, rx, ry=None, *, nccl_id:
         nccl_id = shared_nccl_id()
     if device is None:
         device = int(os.environ.get("LOCAL_RANK", "0"))
-    s = _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
-                           device=device, **kw)
-    if kw.get("peer_halo") and world > 1:
+    peer = kw.pop("peer_halo", False)            # False | True | "auto" (peer stores if CUDA IPC works, else NCCL)
+    s = None
+    if peer and world > 1:
+        ok, err, blob = 1, None, b""
+        try:
+            s = _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
+                                   device=device, peer_halo=True, **kw)
+            blob = s.peer_export()
+        except _solver._lib.HeatError as e:
+            ok, err = 0, e
         # every rank publishes its CUDA-IPC blob; each takes its two neighbours' (replaces MPI_Cart_shift, :103)
         blobs = [None] * world
-        dist.all_gather_object(blobs, s.peer_export())
-        s.peer_attach(blobs[rank - 1] if rank > 0 else None, blobs[rank + 1] if rank + 1 < world else None)
+        dist.all_gather_object(blobs, blob)          # always matched, whatever happened above
+        if ok:
+            up = blobs[rank - 1] if rank > 0 else None
+            down = blobs[rank + 1] if rank + 1 < world else None
+            try:
+                if (rank > 0 and not up) or (rank + 1 < world and not down):
+                    raise _solver._lib.HeatError(-5, "a neighbour could not export its buffers")
+                s.peer_attach(up, down)              # opens the handles; waits for nobody
+            except _solver._lib.HeatError as e:
+                ok, err = 0, e
+        import torch
+        flag = torch.tensor([ok], device="cuda" if dist.get_backend() == "nccl" else "cpu")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            s.halo_mode = "peer stores (CUDA IPC)"
+            return s
+        if s is not None:
+            s.close()
+        if peer != "auto":
+            raise RuntimeError("peer halo unavailable on at least one rank" + ("" if ok else ": %s" % err))
+        nccl_id = shared_nccl_id()                 # a fresh id: the first one may already be consumed
+    s = _solver.HeatSolver(field_slab, rx, ry, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
+                           device=device, **kw)
+    s.halo_mode = "NCCL send/recv" if world > 1 else "none"
     return s

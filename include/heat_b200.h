@@ -130,7 +130,8 @@ int heat_halo_exchange(heat_handle* h);
  * rank's copy engine writes its edge rows straight into the neighbours' ghost rows, which are mapped here
  * through CUDA IPC; ordering uses flag words and stream-ordered waits only.  After heat_init every rank calls
  * heat_peer_export(blob) (HEAT_PEER_BLOB_BYTES bytes), the host layer hands each rank the blobs of rank-1 and
- * rank+1 (NULL at the ends), and heat_peer_attach opens them and performs the first ghost fill (collective).
+ * rank+1 (NULL at the ends), and heat_peer_attach opens them (no cross-GPU wait: the ghosts are filled by the
+ * first heat_step / heat_halo_exchange, which all ranks must then call).
  * cfg.nccl_id may then be NULL (heat_gather with global_root >= 0 still needs it).
  * ref: replaces swap() — pack, 2 x MPI_Sendrecv, unpack — of fortran/mpi+cuda/heat.F90:145-193 entirely. */
 #define HEAT_PEER_BLOB_BYTES 256
