@@ -202,6 +202,8 @@ def main():
                     help="halo exchange: peer stores from the edge-strip kernels over CUDA IPC (auto falls back to NCCL "
                          "if IPC is unavailable) or ncclSend/ncclRecv")
     ap.add_argument("--timesteps", type=int, default=0, help="override time steps per bench step")
+    ap.add_argument("--field", default="hat", choices=["hat", "random"],
+                    help="synthetic input: the reference's hat IC, or seeded uniform [1,2) (guards against value-dependent shortcuts)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -258,6 +260,14 @@ def main():
             field[0] = 1.0
         if row0 + nrows == ny_global:
             field[-1] = 1.0
+    if args.field == "random":
+        interior = (1.0 + np.random.default_rng(1234 + rank).random(field.shape)).astype(dtype)
+        interior[:, 0] = interior[:, -1] = 1.0
+        if row0 == 0:
+            interior[0] = 1.0
+        if row0 + nrows == ny_global:
+            interior[-1] = 1.0
+        field = interior
     pinned = torch.empty(field.shape, dtype=torch.float64 if dtype == np.float64 else torch.float32).pin_memory()
     host_in = pinned.numpy()
     host_in[...] = field
@@ -358,7 +368,7 @@ def main():
             "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": args.workload + ": " + wl["desc"], "nx": nx, "ny_global": ny_global,
                        "timesteps_per_step": timesteps, "kernel": roofline["kernel"], "tblock": args.tblock,
-                       "fmad": bool(args.fmad), "op_order": "fortran",
+                       "fmad": bool(args.fmad), "op_order": "fortran", "field": args.field,
                        "parallelism": "row-slabs x%d" % world + (", ghost %d, overlap %s, halo via %s" % (args.ghost, not args.no_overlap, solver_halo_mode.v) if world > 1 else ""),
                        "l2": "working set %.0f MB per GPU vs 126 MB L2: inputs larger than L2, no flush" % (2 * nrows * nx * esize / 1e6)},
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(total_launches),
