@@ -205,6 +205,7 @@ def main():
     ap.add_argument("--field", default="hat", choices=["hat", "random"],
                     help="synthetic input: the reference's hat IC, or seeded uniform [1,2) (guards against value-dependent shortcuts)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3                       # timing rules: W >= 3
@@ -353,6 +354,25 @@ def main():
     e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": slab_bytes, "d2h_bytes_per_step": slab_bytes,
            "steps": e2e_k, "ms_per_step": e2e_ms / e2e_k}
 
+    # ---- extra, N=1 only: the same workload with 4 time steps fused per HBM round trip (bit-identical results)
+    extras = None
+    if world == 1 and args.tblock == 1 and not args.no_extras:
+        s4 = heatb200.HeatSolver(host_in, r, **{**common, "tblock": 4})
+        for _ in range(2):
+            s4.step(timesteps)
+        k4 = max(2, min(args.steps, 5))
+        ms4 = timed(lambda: s4.step(timesteps), k4)
+
+        def e2e4():
+            s4.set_field(host_in)
+            s4.step(timesteps)
+            s4.gather(out=host_out)
+        e2e4()
+        ems4 = timed(e2e4, k4)
+        s4.close()
+        extras = {"tblock4": {"value": lups_per_step * k4 / (ms4 * 1e-3) / 1e9, "e2e": lups_per_step * k4 / (ems4 * 1e-3) / 1e9,
+                              "unit": UNIT, "note": "temporal blocking k=4, 4 B/LUP algorithmic; same field bits as k=1"}}
+
     total_launches = launches
     if dist is not None:
         t = torch.tensor([float(launches)], dtype=torch.float64, device="cuda")
@@ -374,6 +394,8 @@ def main():
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(total_launches),
             "clocks": clk.summary(),
         }
+        if extras:
+            line["extras"] = extras
         if world > 1:
             line["halo"] = {"last_exchange_ms": halo_ms, "exchanges": int(tm.halo_exchanges)}
         if world == 1 and not args.no_cpu_baseline:
