@@ -66,6 +66,7 @@ struct heat_handle {
     int kernel = HEAT_KERNEL_SIMPLE;
     int tblock = 1;
     bool fma = false;
+    bool vec_ok = false;           // buffers 16-byte aligned and pitch a multiple of the vector width
     int valid_ghost = 0;           // ghost rows of buf[cur] that hold current-time values
     bool comm_pending = false;     // an exchange is in flight on s_comm
     cudaStream_t s_compute = nullptr, s_comm = nullptr;
@@ -119,7 +120,7 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
     if (h->kernel == HEAT_KERNEL_STREAM) {
         constexpr int V = Pack<T>::V;
         const int threads = h->stream_threads ? h->stream_threads : 256;
-        const long nvec = h->pitch / V;
+        const long nvec = h->vec_ok ? h->pitch / V : (long)h->nx - 2;      // lanes needed per row
         const int gx = (int)((nvec + threads - 1) / threads);
         int rpb = h->stream_rows;
         if (rpb <= 0) {
@@ -129,8 +130,12 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
         }
         rpb = std::min(rpb, rows);
         const int gy = (rows + rpb - 1) / rpb;
-        heat_stream_kernel<T, ORDER, FMA, 4><<<dim3(gx, gy), threads, 0, s>>>(
-            S, D, h->nx, h->pitch, yb, ye, rpb, rx, ry);
+        if (h->vec_ok)
+            heat_stream_kernel<T, ORDER, FMA, 4><<<dim3(gx, gy), threads, 0, s>>>(
+                S, D, h->nx, h->pitch, yb, ye, rpb, rx, ry);
+        else        // pitch or base not 16-byte friendly: one cell per lane
+            heat_stream1_kernel<T, ORDER, FMA, 4><<<dim3(gx, gy), threads, 0, s>>>(
+                S, D, 1, h->nx - 1, h->pitch, yb, ye, rpb, rx, ry);
     } else if (h->kernel == HEAT_KERNEL_WTMA) {
         const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;
         return launch_temporal_rows<T, ORDER, FMA, 1>(h->temporal, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch, yb, ye,
@@ -326,18 +331,19 @@ static int resolve_kernel(heat_handle* h) {
                          ((uintptr_t)h->buf[1] % 16 == 0);
     const bool fits_resident = c.nranks == 1 && h->nx >= 3 && h->ny >= 3 &&
                                2 * (size_t)h->nx * h->ny * h->esize <= 200 * 1024;
+    h->vec_ok = aligned;
     int k = c.kernel;
     if (k == HEAT_KERNEL_AUTO) {
         if (fits_resident) k = HEAT_KERNEL_RESIDENT;
         else if (aligned)                            // measured (profiles/): fp64 -> CTA-level TMA kernel at 4096^2 and
             k = (c.dtype == HEAT_F32 && (long)h->nx * h->lrows >= (1L << 26)) ? HEAT_KERNEL_WTMA   // 16384^2; large fp32 ->
                                                                                : HEAT_KERNEL_TMA;  // warp-level pipelines
-        else k = HEAT_KERNEL_SIMPLE;
+        else k = HEAT_KERNEL_STREAM;                 // its one-cell-per-lane variant needs no alignment
     }
     if (k == HEAT_KERNEL_RESIDENT && !fits_resident)
         return fail(HEAT_ERR_UNSUPPORTED, "RESIDENT kernel needs nranks == 1 and 2*nx*ny*sizeof(T) <= 200 KiB");
-    if ((k == HEAT_KERNEL_STREAM || k == HEAT_KERNEL_TMA || k == HEAT_KERNEL_WTMA) && !aligned)
-        return fail(HEAT_ERR_UNSUPPORTED, "STREAM/TMA kernels need 16-byte aligned buffers and a pitch that is a multiple of %d elements", (int)V);
+    if ((k == HEAT_KERNEL_TMA || k == HEAT_KERNEL_WTMA) && !aligned)
+        return fail(HEAT_ERR_UNSUPPORTED, "TMA kernels need 16-byte aligned buffers and a pitch that is a multiple of %d elements", (int)V);
     if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_WTMA) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
     h->kernel = k;
     return HEAT_OK;
@@ -539,7 +545,7 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
 
     if (h->tblock > 1 || h->kernel == HEAT_KERNEL_WTMA) {
         if (h->tblock != 1 && h->tblock != 2 && h->tblock != 4) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: tblock must be 1, 2 or 4"); }
-        if (h->kernel == HEAT_KERNEL_SIMPLE || h->kernel == HEAT_KERNEL_RESIDENT) {
+        if (h->kernel == HEAT_KERNEL_SIMPLE || h->kernel == HEAT_KERNEL_RESIDENT || !h->vec_ok) {
             h->tblock = 1;             // unaligned caller buffers / tiny fields: fall back to single steps
         } else {
             rc = temporal_setup(h->temporal, h->buf, cfg->dtype == HEAT_F32, h->lrows, h->pitch, h->tblock, g_err);

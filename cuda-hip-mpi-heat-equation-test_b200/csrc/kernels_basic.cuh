@@ -6,6 +6,7 @@
 // serve whole fields, multi-GPU slabs with shrinking ghost regions, and boundary strips.
 #pragma once
 #include "stencil_ops.cuh"
+#include "kernels_stream1.cuh"
 
 namespace heat {
 

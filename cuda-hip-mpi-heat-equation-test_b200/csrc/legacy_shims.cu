@@ -4,7 +4,9 @@
 // asynchronous on the default stream, no return value, caller synchronises.
 // ref: fortran/hip/heat_kernel.cpp:26 (idx), :29 (idx_s), :31-61, :63-150.
 #include "../../include/heat_b200.h"
-#include "stencil_ops.cuh"
+
+#include <algorithm>
+#include "kernels_stream1.cuh"
 
 namespace {
 
@@ -49,8 +51,17 @@ extern "C" {
 
 void launch_heat_eqn(double* Td, double* Td_old, double r, int nx, int ny, int ng) {
     if (nx < 1 || ny < 1 || ng < 1) return;
-    dim3 block(128, 2), grid((nx + 127) / 128, (ny + 1) / 2);
-    legacy_heat_eqn_kernel<<<grid, block>>>(Td, Td_old, r, nx, ny, ng);
+    if ((long)nx * ny < (1L << 16)) {      // tiny: one thread per cell
+        dim3 block(128, 2), grid((nx + 127) / 128, (ny + 1) / 2);
+        legacy_heat_eqn_kernel<<<grid, block>>>(Td, Td_old, r, nx, ny, ng);
+        return;
+    }
+    // row-marching scalar kernel on the ghosted array: columns [ng, ng+nx), rows [ng, ng+ny), pitch nx+2ng
+    const int threads = 256, gx = (nx + threads - 1) / threads;
+    const int ychunks = std::max(1, 148 * 16 / gx);
+    const int rpb = std::min(ny, std::max(32, (ny + ychunks - 1) / ychunks));
+    heat::heat_stream1_kernel<double, heat::ORDER_FORTRAN, false, 4><<<dim3(gx, (ny + rpb - 1) / rpb), threads>>>(
+        Td_old, Td, ng, ng + nx, (long)nx + 2 * ng, ng, ng + ny, rpb, r, r);
 }
 
 void launch_send(double* Td, double* Tds1, double* Tds2, int nx, int ny, int ng) {

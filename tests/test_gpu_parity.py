@@ -295,15 +295,23 @@ def test_external_torch_buffers_and_unaligned_pitch():
     b0 = torch.zeros((200, 301), dtype=torch.float64, device="cuda")
     b1 = torch.zeros_like(b0)
     with heatb200.HeatSolver(u0, R100, buffers=(b0, b1)) as s:
-        assert s.kernel_name == "simple"            # pitch 101 is not 16-byte friendly
+        assert s.kernel_name == "stream"            # odd pitch: the one-cell-per-lane variant of STREAM
         s.step(4)
         got = s.gather()
         cur = (b0, b1)[s.info().current]
     assert_bit_equal(got, ho.march(u0, 4, 0, R100))
     assert_bit_equal(cur.cpu().numpy(), got)       # the caller's tensors ARE the storage
     with pytest.raises(heatb200.HeatError) as e:
-        heatb200.HeatSolver(u0, R100, buffers=(b0, b1), kernel="stream")
+        heatb200.HeatSolver(u0, R100, buffers=(b0, b1), kernel="tma")   # TMA needs 16-byte friendly rows
     assert e.value.code == _lib.ERR_UNSUPPORTED
+    for shape in [(3, 3), (40, 35), (130, 257), (77, 1001)]:            # odd pitches through the scalar STREAM kernel
+        v0 = rand_field(shape, seed=shape[1])
+        c0 = torch.zeros(shape, dtype=torch.float64, device="cuda")
+        c1 = torch.zeros_like(c0)
+        for kern in ("stream", "simple"):
+            with heatb200.HeatSolver(v0, R100, 0.2437, order="pyserial", buffers=(c0, c1), kernel=kern, tblock=2) as s2:
+                s2.step(7)
+                assert_bit_equal(s2.gather(), ho.march(v0, 7, ho.ORDER_PYSERIAL, R100, 0.2437))
 
 
 def test_checksum_deterministic_and_close():
@@ -327,6 +335,19 @@ def test_error_paths():
     with heatb200.HeatSolver(u0, 0.25) as s:
         with pytest.raises(heatb200.HeatError):
             s.step(-1)
+
+
+def test_legacy_launcher_large_ghosted_array():
+    """launch_heat_eqn on a ghosted array big enough for its row-marching path (odd pitch nx + 2)."""
+    import ctypes as C
+    import torch
+    nx, ny, ng = 1000, 300, 1
+    g0 = rand_field((ny + 2, nx + 2), seed=77)
+    old = torch.from_numpy(g0).cuda()
+    new = old.clone()
+    heatb200.lib().launch_heat_eqn(C.c_void_p(new.data_ptr()), C.c_void_p(old.data_ptr()), R100, nx, ny, ng)
+    torch.cuda.synchronize()
+    assert_bit_equal(new.cpu().numpy(), ho.march(g0, 1, ho.ORDER_FORTRAN, R100))
 
 
 def test_legacy_hip_abi(golden):
