@@ -49,6 +49,8 @@ def main():
         s = hd.slab_solver(full[r0:r0 + nr], ny, R100, 0.2437, nccl_id=nccl_id, device=local, order="pyserial",
                            kernel=kernel, tblock=k, ghost=g, overlap=overlap, peer_halo=peer)
         s.step(steps // 2)
+        if ci % 2:
+            s.halo_exchange()                      # an explicit, extra exchange must change nothing (heat_halo_exchange)
         s.step(steps - steps // 2)                 # split: exercises ghost state carried between calls
         got = s.gather(root=0)
         local_rows = s.gather()
