@@ -55,8 +55,6 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
     if (pdl_early) pdl_launch_dependents();
     if (item_fwd >= nitems) return;               // whole warps leave; nothing below syncs across warps
     const int item = (kflags & KF_REVERSE) ? nitems - 1 - item_fwd : item_fwd;
-    const bool ld_hint = kflags & KF_LOAD_EVICT_FIRST, st_hinted = kflags & KF_STORE_EVICT_LAST;
-    const uint64_t pol_ld = policy_evict_first(), pol_st = policy_evict_last();
     const int strip = item % nstrips, seg = item / nstrips;
     const int xs = strip * WOUT - HX;             // first column of the loaded strip
     const int ys = y_begin + seg * seg_rows;
@@ -70,8 +68,7 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
     auto issue = [&](int j) {
         const int slot = j % S;
         mbar_expect_tx(&full[slot], kStageBytes);
-        if (ld_hint) tma_load_2d_hint(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot], pol_ld);
-        else tma_load_2d(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot]);
+        tma_load_2d(ring + (size_t)slot * RS * WIN, &tmap, xs, ys - K + j * RS, &full[slot]);
     };
     if (lane == 0) {
 #pragma unroll
@@ -161,8 +158,7 @@ heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ d
                         P out;
 #pragma unroll
                         for (int i = 0; i < V; ++i) out.v[i] = outrow[m * V + i];
-                        if (st_hinted) st_hint(orow + m * V, out, pol_st);
-                        else *reinterpret_cast<P*>(orow + m * V) = out;
+                        *reinterpret_cast<P*>(orow + m * V) = out;
                         if (dst2)   // peer store into the neighbour GPU's ghost row (see kernels_tma.cuh)
                             *reinterpret_cast<P*>(dst2 + (long)(o + shift2) * pitch + xl + m * V) = out;
                     }
