@@ -109,7 +109,7 @@ template <typename T, int ORDER, bool FMA>
 __global__ void __launch_bounds__(1024)
 heat_resident_kernel(const T* __restrict__ src, T* __restrict__ dst, int nx, int ny, long pitch,
                      int nt, T rx, T ry) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     T* a = reinterpret_cast<T*>(smem_raw);
     T* b = a + (long)nx * ny;
     const int cells = nx * ny;
