@@ -335,9 +335,7 @@ static int resolve_kernel(heat_handle* h) {
     int k = c.kernel;
     if (k == HEAT_KERNEL_AUTO) {
         if (fits_resident) k = HEAT_KERNEL_RESIDENT;
-        else if (aligned)                            // measured (profiles/): fp64 -> CTA-level TMA kernel at 4096^2 and
-            k = (c.dtype == HEAT_F32 && (long)h->nx * h->lrows >= (1L << 26)) ? HEAT_KERNEL_WTMA   // 16384^2; large fp32 ->
-                                                                               : HEAT_KERNEL_TMA;  // warp-level pipelines
+        else if (aligned) k = HEAT_KERNEL_TMA;       // measured fastest for fp64 and fp32 at 4096^2 and 16384^2 (profiles/)
         else k = HEAT_KERNEL_STREAM;                 // its one-cell-per-lane variant needs no alignment
     }
     if (k == HEAT_KERNEL_RESIDENT && !fits_resident)

@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <string>
+#include <type_traits>
 
 #include "stencil_ops.cuh"
 
@@ -256,27 +257,37 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
     // lanes at a warp's edge read the adjacent cell from shared memory instead of shuffling
     const int sxe = (lane == 0) ? sx - 1 : sx + V;
 
-    for (int j = 0; j < nstages; ++j) {
-        mbar_wait(&full[j % S], (unsigned)((j / S) & 1));
+    // A stage is PLAIN when none of its rows needs a guard: every row it reads has been loaded, every row it
+    // produces lies inside this CTA's segment, the strip touches no Dirichlet column and no pitch padding, and
+    // no cache-policy or mirror store is requested.  Plain stages — almost all of them — run a copy of the body
+    // without the selects, predicates and signed index arithmetic (fewer instructions, less power).
+    const bool plain_cta = x0 >= V && (long)x0 + BX <= (long)nx - 1 && (long)x0 + BX <= pitch && !st_hinted && !dst2;
+    static_assert((RING & (RING - 1)) == 0, "ring depth must be a power of two");
+
+    auto stage_body = [&](auto plain_tag, int j) {
+        constexpr bool PLAIN = decltype(plain_tag)::value;
         const int p0 = j * BY - 1 + sub * RPS;      // first centre row of this subgroup
         P win[RPS + 2];
         T edg[RPS];
 #pragma unroll
         for (int i = 0; i < RPS + 2; ++i) {
             const int p = p0 - 1 + i;
-            if (p >= 0) win[i] = *reinterpret_cast<const P*>(ring + (size_t)(p % RING) * BW + sx);
+            if (PLAIN || p >= 0) win[i] = *reinterpret_cast<const P*>(ring + (size_t)((unsigned)p & (RING - 1)) * BW + sx);
             else {
 #pragma unroll
                 for (int v = 0; v < V; ++v) win[i].v[v] = T(0);
             }
         }
+        if (lane == 0 || lane == 31) {
 #pragma unroll
-        for (int i = 0; i < RPS; ++i) {
-            const int p = p0 + i;
-            edg[i] = (p >= 0 && (lane == 0 || lane == 31)) ? ring[(size_t)(p % RING) * BW + sxe] : T(0);
+            for (int i = 0; i < RPS; ++i) {
+                const int p = p0 + i;
+                edg[i] = (PLAIN || p >= 0) ? ring[(size_t)((unsigned)p & (RING - 1)) * BW + sxe] : T(0);
+            }
         }
+        T* q = dst + (long)(ys - 1 + p0) * pitch + xg;
 #pragma unroll
-        for (int i = 0; i < RPS; ++i) {
+        for (int i = 0; i < RPS; ++i, q += pitch) {
             const int p = p0 + i;
             const P& s = win[i];
             const P& c = win[i + 1];
@@ -291,16 +302,28 @@ heat_tma_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, i
                 const T w = (v == 0) ? left : c.v[v - 1];
                 const T e = (v == V - 1) ? right : c.v[v + 1];
                 const T r = stencil<T, ORDER, FMA>(c.v[v], w, e, s.v[v], n.v[v], rx, ry);
-                const long x = xg + v;
-                o.v[v] = (x >= 1 && x <= nx - 2) ? r : c.v[v];
+                if constexpr (PLAIN) o.v[v] = r;
+                else {
+                    const long x = xg + v;
+                    o.v[v] = (x >= 1 && x <= nx - 2) ? r : c.v[v];
+                }
             }
-            if (active && p >= 1 && p <= np) {
-                T* q = dst + (long)(ys - 1 + p) * pitch + xg;
+            if constexpr (PLAIN) {
+                *reinterpret_cast<P*>(q) = o;
+            } else if (active && p >= 1 && p <= np) {
                 if (st_hinted) st_hint(q, o, pol_st);
                 else *reinterpret_cast<P*>(q) = o;
                 if (dst2) *reinterpret_cast<P*>(dst2 + (long)(ys - 1 + p + shift2) * pitch + xg) = o;
             }
         }
+    };
+
+    for (int j = 0; j < nstages; ++j) {
+        mbar_wait(&full[j % S], (unsigned)((j / S) & 1));
+        // rows produced by stage j: p = j*BY-1 .. (j+1)*BY-2, all inside [1, np] and all inputs loaded?
+        const bool plain = plain_cta && j >= 1 && (j + 1) * BY - 2 <= np;
+        if (plain) stage_body(std::true_type{}, j);
+        else stage_body(std::false_type{}, j);
         __syncthreads();                            // everyone is done with stage j-1 (and j's reads)
         if (tid == 0 && j + S - 1 < nstages) issue(j + S - 1);
     }
