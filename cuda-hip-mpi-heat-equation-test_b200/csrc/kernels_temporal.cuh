@@ -4,7 +4,7 @@
 // lane 0 streams (32*M*V) x RS boxes of the time-level-0 field into the warp's own ring of S
 // shared-memory stages (cp.async.bulk.tensor.2d + one mbarrier per stage); nothing in the kernel
 // synchronises wider than a warp.  Each lane owns M*V contiguous cells of the strip and keeps, for
-// every time level 0..K-1, the two previous rows in registers.  When level-0 row y arrives the
+// every time level 0..K-1, three consecutive rows in registers (their roles rotate, nothing is copied).  When level-0 row y arrives the
 // warp produces level-1 row y-1, level-2 row y-2, ... level-K row y-K (a wavefront skewed along
 // y), exchanging only the two lane-edge cells per level by warp shuffle, and stores level K.
 // The field therefore crosses HBM once per K steps: 16/K B per lattice update (fp64) plus the
@@ -187,8 +187,6 @@ struct TemporalState {
     int k = 0, m = 0;
     bool ready = false;
 };
-
-template <typename T> constexpr int temporal_m() { return 2; }
 
 inline int temporal_setup(TemporalState& st, void* const buf[2], bool f32, int rows, long pitch, int k,
                           std::string& err) {
