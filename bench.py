@@ -402,10 +402,12 @@ def main():
             cnx = min(nx, 4096)
             g, cores, st, dt = cpu_march_glups(cnx, cnx, budget_s=12.0)
             gn, stn = numpy_reference_glups(cnx, cnx, budget_s=5.0)
+            g1, _, st1, dt1 = cpu_march_glups(cnx, cnx, budget_s=4.0, threads_all=False)
             line["cpu_baseline"] = {
                 "value": g, "unit": UNIT, "cores": cores, "kind": "port",
                 "sample": "%dx%d fp64, %d timesteps in %.1f s: C port of the fortran/serial loop, OpenMP on %d cores" % (cnx, cnx, st, dt, cores),
-                "numpy_1thread": {"value": gn, "sample": "python/serial expression (heat.py:49-58) in NumPy, %dx%d, %d steps" % (cnx, cnx, stn)}}
+                "numpy_1thread": {"value": gn, "sample": "python/serial expression (heat.py:49-58) in NumPy, %dx%d, %d steps" % (cnx, cnx, stn)},
+                "c_port_1thread": {"value": g1, "sample": "same C port, 1 thread (the reference's CPU programs are serial), %dx%d, %d steps in %.1f s" % (cnx, cnx, st1, dt1)}}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
