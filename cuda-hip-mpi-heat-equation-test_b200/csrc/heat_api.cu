@@ -301,15 +301,19 @@ static int exchange(heat_handle* h, int which, cudaStream_t s) {
     const int up = h->cfg.rank - 1, down = h->cfg.rank + 1;
     CUDA_TRY(cudaEventRecord(h->ev_h0, s));
     NCCL_TRY(N.GroupStart());
+    ncclResult_t gr = 0;                       // first failure inside the group; the group is closed regardless
+    auto in_group = [&](ncclResult_t r) { if (gr == 0) gr = r; };
     if (up >= 0) {
-        NCCL_TRY(N.Send(row_ptr(h, which, h->g), count, dt, up, h->comm, s));
-        NCCL_TRY(N.Recv(row_ptr(h, which, 0), count, dt, up, h->comm, s));
+        in_group(N.Send(row_ptr(h, which, h->g), count, dt, up, h->comm, s));
+        in_group(N.Recv(row_ptr(h, which, 0), count, dt, up, h->comm, s));
     }
     if (down < h->cfg.nranks) {
-        NCCL_TRY(N.Send(row_ptr(h, which, h->nrows), count, dt, down, h->comm, s));
-        NCCL_TRY(N.Recv(row_ptr(h, which, h->g + h->nrows), count, dt, down, h->comm, s));
+        in_group(N.Send(row_ptr(h, which, h->nrows), count, dt, down, h->comm, s));
+        in_group(N.Recv(row_ptr(h, which, h->g + h->nrows), count, dt, down, h->comm, s));
     }
-    NCCL_TRY(N.GroupEnd());
+    const ncclResult_t ge = N.GroupEnd();
+    if (gr != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclSend/ncclRecv failed: %s", N.GetErrorString(gr));
+    if (ge != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclGroupEnd failed: %s", N.GetErrorString(ge));
     CUDA_TRY(cudaEventRecord(h->ev_h1, s));
     h->halo_timed = true;
     return HEAT_OK;
@@ -384,7 +388,10 @@ int heat_derive_fortran(int n, double sigma, double nu, double dom_len, double* 
 int heat_nccl_unique_id(void* out128) {
     if (!out128) return fail(HEAT_ERR_INVALID, "heat_nccl_unique_id: null output");
     const NcclApi& N = nccl_api();
-    if (!N.ok) return fail(HEAT_ERR_NCCL, "NCCL not available: %s", dlerror() ? dlerror() : "libnccl.so.2 not found");
+    if (!N.ok) {
+        const char* why = dlerror();             // reading it clears it: read once
+        return fail(HEAT_ERR_NCCL, "NCCL not available: %s", why ? why : "libnccl.so.2 not found");
+    }
     ncclUniqueId id;
     NCCL_TRY(N.GetUniqueId(&id));
     memcpy(out128, &id, sizeof id);
@@ -452,7 +459,8 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     if (cfg->op_order < 0 || cfg->op_order > 2) return fail(HEAT_ERR_INVALID, "heat_init: bad op_order %d", cfg->op_order);
     if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks)
         return fail(HEAT_ERR_INVALID, "heat_init: bad rank %d of %d", cfg->rank, cfg->nranks);
-    if (cfg->tblock < 0 || cfg->tblock > 8) return fail(HEAT_ERR_INVALID, "heat_init: tblock must be in 0..8");
+    if (cfg->tblock != 0 && cfg->tblock != 1 && cfg->tblock != 2 && cfg->tblock != 4)
+        return fail(HEAT_ERR_INVALID, "heat_init: tblock must be 0 (= 1), 1, 2 or 4 (got %d)", cfg->tblock);
     if (cfg->nranks > 1 && !cfg->nccl_id && !(cfg->flags & (HEAT_FLAG_SKIP_EXCHANGE | HEAT_FLAG_PEER_HALO)))
         return fail(HEAT_ERR_INVALID, "heat_init: nranks > 1 needs cfg.nccl_id (or HEAT_FLAG_PEER_HALO)");
     if ((cfg->ext_buf[0] == nullptr) != (cfg->ext_buf[1] == nullptr))
@@ -479,9 +487,12 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     int rc = heat_slab_partition(h->ny, cfg->nranks, cfg->rank, &h->row0, &h->nrows);
     if (rc) { delete h; return rc; }
     h->g = cfg->nranks > 1 ? (cfg->ghost > 0 ? cfg->ghost : 1) : 0;
-    if (cfg->nranks > 1 && h->nrows < h->g) {
+    // judged on the THINNEST slab of the partition, not on this rank's: every rank then takes the same
+    // decision and none is left waiting inside the collective calls below
+    if (cfg->nranks > 1 && h->ny / cfg->nranks < h->g) {
         delete h;
-        return fail(HEAT_ERR_INVALID, "heat_init: slab of %d rows is thinner than ghost depth %d", h->nrows, h->g);
+        return fail(HEAT_ERR_INVALID, "heat_init: the thinnest slab (%d rows of %d over %d ranks) is thinner than ghost depth %d",
+                    cfg->ny / cfg->nranks, cfg->ny, cfg->nranks, cfg->ghost > 0 ? cfg->ghost : 1);
     }
     if (h->g % h->tblock != 0 && cfg->nranks > 1) {
         delete h;
@@ -542,7 +553,6 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     }
 
     if (h->tblock > 1 || h->kernel == HEAT_KERNEL_WTMA) {
-        if (h->tblock != 1 && h->tblock != 2 && h->tblock != 4) { heat_destroy(h); return fail(HEAT_ERR_UNSUPPORTED, "heat_init: tblock must be 1, 2 or 4"); }
         if (h->kernel == HEAT_KERNEL_SIMPLE || h->kernel == HEAT_KERNEL_RESIDENT || !h->vec_ok) {
             h->tblock = 1;             // unaligned caller buffers / tiny fields: fall back to single steps
         } else {
@@ -809,10 +819,8 @@ int heat_checksum(heat_handle* h, double* sum) {
     CUDA_TRY(cudaSetDevice(h->dev));
     int rc = wait_comm(h);
     if (rc) return rc;
-    if (!h->d_partials) {
-        CUDA_TRY(cudaMalloc(&h->d_partials, kSumBlocks * sizeof(double)));
-        CUDA_TRY(cudaMalloc(&h->d_sum, sizeof(double)));
-    }
+    if (!h->d_partials) CUDA_TRY(cudaMalloc(&h->d_partials, kSumBlocks * sizeof(double)));
+    if (!h->d_sum) CUDA_TRY(cudaMalloc(&h->d_sum, sizeof(double)));
     const int yb = h->g, ye = h->g + h->nrows;
     if (h->cfg.dtype == HEAT_F32)
         heat_sum_partial_kernel<float><<<kSumBlocks, 256, 0, h->s_compute>>>((const float*)h->buf[h->cur], h->nx, h->pitch, yb, ye, h->d_partials);

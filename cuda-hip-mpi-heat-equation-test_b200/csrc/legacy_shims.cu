@@ -3,32 +3,47 @@
 // against libheat.so unchanged: ghosted i-contiguous arrays, caller-owned device buffers,
 // asynchronous on the default stream, no return value, caller synchronises.
 // ref: fortran/hip/heat_kernel.cpp:26 (idx), :29 (idx_s), :31-61, :63-150.
+//
+// Both flavours of the reference's `real` (heat_kernel.cpp:5-9) are exported: the double one under the
+// reference's own names, the -DSINGLE_PRECISION one under the same names with an `_sp` suffix (one
+// library cannot carry two `launch_heat_eqn`; include/heat_b200.h maps the plain names onto the `_sp`
+// ones when SINGLE_PRECISION is defined, as the reference's macro does).
 #include "../../include/heat_b200.h"
 
 #include <algorithm>
+#include <atomic>
+
+#include <cuda_runtime.h>
+
 #include "kernels_stream1.cuh"
 
 namespace {
+
+// heat_legacy_set_fmad: 0 (default) = every add/mul rounded separately — the kernel text read literally,
+// what the goldens built with -ffp-contract=off hold; 1 = c + r*(t - 4c) fused the way hipcc's default
+// -ffp-contract=fast (and nvcc's -fmad=true) compile that same text.
+std::atomic<int> g_legacy_fmad{0};
 
 // element (i, j), 1-based interior, of a ghosted array: (i-1+ng) + (nx+2ng)*(j-1+ng)
 __device__ __forceinline__ long gidx(int i, int j, int nx, int ng) {
     return (long)(i - 1 + ng) + (long)(nx + 2 * ng) * (j - 1 + ng);
 }
 
+template <typename T, bool FMA>
 __global__ void __launch_bounds__(256)
-legacy_heat_eqn_kernel(double* __restrict__ Td, const double* __restrict__ Td_old, double r, int nx, int ny, int ng) {
+legacy_heat_eqn_kernel(T* __restrict__ Td, const T* __restrict__ Td_old, T r, int nx, int ny, int ng) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
     const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
     if (i > nx || j > ny) return;
     const long w = nx + 2 * ng;
-    const double* p = Td_old + gidx(i, j, nx, ng);
-    Td[gidx(i, j, nx, ng)] =
-        heat::stencil<double, heat::ORDER_FORTRAN, false>(p[0], p[-1], p[1], p[-w], p[w], r, r);
+    const T* p = Td_old + gidx(i, j, nx, ng);
+    Td[gidx(i, j, nx, ng)] = heat::stencil<T, heat::ORDER_FORTRAN, FMA>(p[0], p[-1], p[1], p[-w], p[w], r, r);
 }
 
 // which: 0 = pack both edge lines, 1 = unpack into the low ghost, 2 = unpack into the high ghost
+template <typename T>
 __global__ void __launch_bounds__(256)
-legacy_swap_kernel(double* __restrict__ Td, double* __restrict__ a, double* __restrict__ b, int nx, int ny, int ng, int which) {
+legacy_swap_kernel(T* __restrict__ Td, T* __restrict__ a, T* __restrict__ b, int nx, int ny, int ng, int which) {
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (long)ng * ny) return;
     const int i = (int)(t % ng) + 1, j = (int)(t / ng) + 1;
@@ -45,38 +60,60 @@ legacy_swap_kernel(double* __restrict__ Td, double* __restrict__ a, double* __re
 
 inline unsigned blocks_for(long n) { return (unsigned)((n + 255) / 256); }
 
-}  // namespace
+int current_sm_count() {                   // per device, looked up once (the launchers have no handle to keep it in)
+    static int cached[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
 
-extern "C" {
-
-void launch_heat_eqn(double* Td, double* Td_old, double r, int nx, int ny, int ng) {
-    if (nx < 1 || ny < 1 || ng < 1) return;
+template <typename T, bool FMA>
+void heat_eqn_t(T* Td, T* Td_old, T r, int nx, int ny, int ng) {
     if ((long)nx * ny < (1L << 16)) {      // tiny: one thread per cell
         dim3 block(128, 2), grid((nx + 127) / 128, (ny + 1) / 2);
-        legacy_heat_eqn_kernel<<<grid, block>>>(Td, Td_old, r, nx, ny, ng);
+        legacy_heat_eqn_kernel<T, FMA><<<grid, block>>>(Td, Td_old, r, nx, ny, ng);
         return;
     }
     // row-marching scalar kernel on the ghosted array: columns [ng, ng+nx), rows [ng, ng+ny), pitch nx+2ng
     const int threads = 256, gx = (nx + threads - 1) / threads;
-    const int ychunks = std::max(1, 148 * 16 / gx);
+    const int ychunks = std::max(1, current_sm_count() * 16 / gx);
     const int rpb = std::min(ny, std::max(32, (ny + ychunks - 1) / ychunks));
-    heat::heat_stream1_kernel<double, heat::ORDER_FORTRAN, false, 4><<<dim3(gx, (ny + rpb - 1) / rpb), threads>>>(
+    heat::heat_stream1_kernel<T, heat::ORDER_FORTRAN, FMA, 4><<<dim3(gx, (ny + rpb - 1) / rpb), threads>>>(
         Td_old, Td, ng, ng + nx, (long)nx + 2 * ng, ng, ng + ny, rpb, r, r);
 }
 
-void launch_send(double* Td, double* Tds1, double* Tds2, int nx, int ny, int ng) {
+template <typename T>
+void heat_eqn(T* Td, T* Td_old, T r, int nx, int ny, int ng) {
     if (nx < 1 || ny < 1 || ng < 1) return;
-    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tds1, Tds2, nx, ny, ng, 0);
+    if (g_legacy_fmad.load(std::memory_order_relaxed)) heat_eqn_t<T, true>(Td, Td_old, r, nx, ny, ng);
+    else heat_eqn_t<T, false>(Td, Td_old, r, nx, ny, ng);
 }
 
-void launch_recv1(double* Td, double* Tdr, int nx, int ny, int ng) {
+template <typename T>
+void swap_op(T* Td, T* a, T* b, int nx, int ny, int ng, int which) {
     if (nx < 1 || ny < 1 || ng < 1) return;
-    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tdr, nullptr, nx, ny, ng, 1);
+    legacy_swap_kernel<T><<<blocks_for((long)ng * ny), 256>>>(Td, a, b, nx, ny, ng, which);
 }
 
-void launch_recv2(double* Td, double* Tdr, int nx, int ny, int ng) {
-    if (nx < 1 || ny < 1 || ng < 1) return;
-    legacy_swap_kernel<<<blocks_for((long)ng * ny), 256>>>(Td, Tdr, nullptr, nx, ny, ng, 2);
-}
+}  // namespace
+
+extern "C" {
+
+int heat_legacy_set_fmad(int on) { return g_legacy_fmad.exchange(on ? 1 : 0); }
+
+void launch_heat_eqn(double* Td, double* Td_old, double r, int nx, int ny, int ng) { heat_eqn(Td, Td_old, r, nx, ny, ng); }
+void launch_send(double* Td, double* Tds1, double* Tds2, int nx, int ny, int ng) { swap_op(Td, Tds1, Tds2, nx, ny, ng, 0); }
+void launch_recv1(double* Td, double* Tdr, int nx, int ny, int ng) { swap_op<double>(Td, Tdr, nullptr, nx, ny, ng, 1); }
+void launch_recv2(double* Td, double* Tdr, int nx, int ny, int ng) { swap_op<double>(Td, Tdr, nullptr, nx, ny, ng, 2); }
+
+void launch_heat_eqn_sp(float* Td, float* Td_old, float r, int nx, int ny, int ng) { heat_eqn(Td, Td_old, r, nx, ny, ng); }
+void launch_send_sp(float* Td, float* Tds1, float* Tds2, int nx, int ny, int ng) { swap_op(Td, Tds1, Tds2, nx, ny, ng, 0); }
+void launch_recv1_sp(float* Td, float* Tdr, int nx, int ny, int ng) { swap_op<float>(Td, Tdr, nullptr, nx, ny, ng, 1); }
+void launch_recv2_sp(float* Td, float* Tdr, int nx, int ny, int ng) { swap_op<float>(Td, Tdr, nullptr, nx, ny, ng, 2); }
 
 }  // extern "C"

@@ -81,6 +81,11 @@ PROTOTYPES = {
     "launch_send": (None, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "launch_recv1": (None, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "launch_recv2": (None, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "launch_heat_eqn_sp": (None, [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int]),
+    "launch_send_sp": (None, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "launch_recv1_sp": (None, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "launch_recv2_sp": (None, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "heat_legacy_set_fmad": (C.c_int, [C.c_int]),
 }
 
 _lib = None

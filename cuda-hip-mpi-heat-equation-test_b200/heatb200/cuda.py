@@ -43,6 +43,8 @@ YDir = nx
 
 kernel = "auto"
 device = 0
+fmad = False        # True: fuse u1 + r*(...) as nvcc does for the reference's kernel string by default
+                    # (PyCUDA SourceModule -> nvcc -fmad=true, cuda.py:86); False: the text read literally
 MAX_THREADS_PER_BLOCK = 1024     # what cuda.py:27 prints on every CUDA device since sm_20
 
 
@@ -100,7 +102,7 @@ def heatCalculate(u_new_arg, u_old_arg, block=(32, 8, 1), grid=None):
     new = u_new_arg.array if isinstance(u_new_arg, (InOut, In)) else u_new_arg
     old = u_old_arg.array if isinstance(u_old_arg, (InOut, In)) else u_old_arg
     old2 = np.ascontiguousarray(old, dtype=np.float64).reshape(ny, nx)
-    with _HeatSolver(old2, r, order="pycuda", kernel=kernel, device=device) as s:
+    with _HeatSolver(old2, r, order="pycuda", kernel=kernel, device=device, fmad=fmad) as s:
         s.step(1)
         res = s.gather()
     new.reshape(ny, nx)[1:-1, 1:-1] = res[1:-1, 1:-1]
@@ -112,7 +114,7 @@ def run(steps=None):
     if u_new is None:
         _alloc()
     steps = nt + 1 if steps is None else steps
-    with _HeatSolver(u_new, r, order="pycuda", kernel=kernel, device=device) as s:
+    with _HeatSolver(u_new, r, order="pycuda", kernel=kernel, device=device, fmad=fmad) as s:
         s.step(steps)
         s.gather(out=u_new)
     u_old = u_new                      # cuda.py:97 leaves them aliased

@@ -55,8 +55,16 @@ extern "C" {
                                    (the temporal-blocking kernel, also used for single steps)     */
 
 /* flags */
-#define HEAT_FLAG_FMAD          1u  /* allow FMA contraction (faster, <=1e-12 rel. off the oracle); default is
-                                       bit-exact: every add/mul individually rounded, as gfortran -O0 / NumPy */
+#define HEAT_FLAG_FMAD          1u  /* FMA contraction.  Default (flag clear) is every add/mul individually rounded:
+                                       bit-exact with the reference's CPU programs (gfortran -O0, NumPy) and with its
+                                       GPU kernel text read literally (goldens built with -ffp-contract=off).
+                                       With the flag, FORTRAN and PYCUDA orders evaluate fma(r, fma(-4,C,t), C) —
+                                       bit-exact with what the reference's GPU toolchains make of that text by default
+                                       (nvcc -fmad=true under PyCUDA, hipcc -ffp-contract=fast; goldens *_fma, built
+                                       with gcc -mfma -ffp-contract=fast — a run of the nvcc/hipcc binaries themselves
+                                       is not available here, so that pairing stays unpinned) and <= 1e-12 relative
+                                       off the uncontracted result; PYSERIAL (NumPy never contracts) has no
+                                       reference counterpart under this flag: <= 1e-12 only */
 #define HEAT_FLAG_OVERLAP       2u  /* nranks>1: exchange halos on a second stream behind the interior update */
 #define HEAT_FLAG_SKIP_EXCHANGE 4u  /* DIAGNOSTIC: no halo traffic (wrong results) — to measure halo time share */
 #define HEAT_FLAG_PEER_HALO     8u  /* nranks>1: neighbours' rows are written by peer stores (CUDA IPC) instead of NCCL */
@@ -161,7 +169,9 @@ int heat_checksum(heat_handle* h, double* sum);
  * more than 1024 (the array's capacity) is refused with HEAT_ERR_UNSUPPORTED.  The first call on each
  * device looks up the array's device address; make that call outside any stream capture.  All
  * calls share the one array (whatever the previous call left in it is overwritten before it is read),
- * so two calls that may overlap on the same GPU — different streams or threads — race: serialise them. */
+ * so two calls that may overlap on the same GPU — different streams or threads — race: serialise them.
+ * The looked-up address is remembered per device for the life of the process; it does not survive
+ * cudaDeviceReset() (do not call this entry point on a device after resetting it). */
 int heat_checksum_noalloc(const void* field_dev, int dtype, int nx, int ny, int64_t pitch,
                           int nblocks, double* sum_dev, uint64_t stream);
 
@@ -190,13 +200,31 @@ int heat_nccl_unique_id(void* out128);
 /* ---- One-shot, caller-owned buffers -------------------------------------------------------- */
 
 /* Legacy launchers with the reference's exact signatures on ghosted, i-contiguous DEVICE arrays
- * ((nx+2ng) x (ny+2ng) doubles, element (i,j) at (i-1+ng) + (nx+2ng)*(j-1+ng)); asynchronous on the
+ * ((nx+2ng) x (ny+2ng) reals, element (i,j) at (i-1+ng) + (nx+2ng)*(j-1+ng)); asynchronous on the
  * default stream, return nothing, caller synchronises — as the originals.
- * ref: fortran/hip/heat_kernel.cpp:48-61, 137-150, 78-90, 106-118; bind(c) fortran/hip/heat.F90:48-102. */
+ * ref: fortran/hip/heat_kernel.cpp:48-61, 137-150, 78-90, 106-118; bind(c) fortran/hip/heat.F90:48-102.
+ * `real` is double, or float when the caller compiles with -DSINGLE_PRECISION, as in the reference
+ * (heat_kernel.cpp:5-9): the float flavour is exported as launch_*_sp and the macros below give it
+ * the reference's names (Fortran: bind(c, name="launch_heat_eqn_sp")). */
 void launch_heat_eqn(double* Td, double* Td_old, double r, int nx, int ny, int ng);
 void launch_send(double* Td, double* Tds1, double* Tds2, int nx, int ny, int ng);
 void launch_recv1(double* Td, double* Tdr, int nx, int ny, int ng);
 void launch_recv2(double* Td, double* Tdr, int nx, int ny, int ng);
+void launch_heat_eqn_sp(float* Td, float* Td_old, float r, int nx, int ny, int ng);
+void launch_send_sp(float* Td, float* Tds1, float* Tds2, int nx, int ny, int ng);
+void launch_recv1_sp(float* Td, float* Tdr, int nx, int ny, int ng);
+void launch_recv2_sp(float* Td, float* Tdr, int nx, int ny, int ng);
+#if defined(SINGLE_PRECISION) && !defined(HEAT_B200_NO_LEGACY_MACROS)
+#define launch_heat_eqn launch_heat_eqn_sp
+#define launch_send     launch_send_sp
+#define launch_recv1    launch_recv1_sp
+#define launch_recv2    launch_recv2_sp
+#endif
+
+/* Process-wide switch for launch_heat_eqn[_sp]: 0 (default) rounds every add/mul separately (the
+ * kernel text read literally); 1 fuses c + r*(t - 4c) the way hipcc compiles heat_kernel.cpp:43 by
+ * default (-ffp-contract=fast).  Returns the previous setting.  ref: fortran/hip/Makefile (hipcc flags). */
+int heat_legacy_set_fmad(int on);
 
 #ifdef __cplusplus
 }

@@ -31,6 +31,9 @@ def lib(omp: bool = False):
     L = _load("liboracle_omp.so" if omp else "liboracle.so")
     L.oracle_march_f64.argtypes = [_dp, C.c_int, C.c_int, C.c_size_t, C.c_double, C.c_double, C.c_int, C.c_int]
     L.oracle_march_f32.argtypes = [_fp, C.c_int, C.c_int, C.c_size_t, C.c_float, C.c_float, C.c_int, C.c_int]
+    L.oracle_march_ex_f64.argtypes = L.oracle_march_f64.argtypes + [C.c_int]
+    L.oracle_march_ex_f32.argtypes = L.oracle_march_f32.argtypes + [C.c_int]
+    L.oracle_threads.argtypes = [C.c_int]
     L.oracle_ic_fortran.argtypes = [_dp, C.c_int, C.c_size_t, C.c_double, C.c_double]
     L.oracle_derive_fortran.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, _dp, _dp, _dp]
     L.oracle_sum_f64.argtypes = [_dp, C.c_int, C.c_int, C.c_size_t]
@@ -38,16 +41,23 @@ def lib(omp: bool = False):
     return L
 
 
-def march(u0: np.ndarray, steps: int, order: int, rx, ry=None, omp: bool = False) -> np.ndarray:
-    """C oracle time-march on a copy of ``u0`` ([ny, nx] float64 or float32)."""
+def threads(n: int = 0, omp: bool = True) -> int:
+    """Threads a march of the OpenMP build will use; n > 0 sets that count first (overriding whatever
+    OMP_NUM_THREADS the launcher exported — torchrun sets it to 1)."""
+    return int(lib(omp).oracle_threads(int(n)))
+
+
+def march(u0: np.ndarray, steps: int, order: int, rx, ry=None, omp: bool = False, contract: bool = False) -> np.ndarray:
+    """C oracle time-march on a copy of ``u0`` ([ny, nx] float64 or float32).  ``contract``: the FMA-fused
+    reading of orders F and C that nvcc / hipcc give the reference's kernel text by default."""
     ry = rx if ry is None else ry
     u = np.ascontiguousarray(u0).copy()
     ny, nx = u.shape
     L = lib(omp)
     if u.dtype == np.float64:
-        rc = L.oracle_march_f64(u.ctypes.data_as(_dp), nx, ny, nx, rx, ry, order, steps)
+        rc = L.oracle_march_ex_f64(u.ctypes.data_as(_dp), nx, ny, nx, rx, ry, order, steps, int(contract))
     elif u.dtype == np.float32:
-        rc = L.oracle_march_f32(u.ctypes.data_as(_fp), nx, ny, nx, rx, ry, order, steps)
+        rc = L.oracle_march_ex_f32(u.ctypes.data_as(_fp), nx, ny, nx, rx, ry, order, steps, int(contract))
     else:
         raise TypeError(u.dtype)
     if rc != 0:
@@ -70,13 +80,15 @@ def derive_fortran(n, sigma, nu, dom_len):
 
 # ------------------------------------------------------------------ reference kernels on the host
 def ref_available() -> bool:
-    return all(os.path.isfile(os.path.join(HERE, "_ref", f)) for f in ("libhipref.so", "libpycudaref.so"))
+    return all(os.path.isfile(os.path.join(HERE, "_ref", f)) for f in
+               ("libhipref.so", "libpycudaref.so", "libhipref_fma.so", "libpycudaref_fma.so"))
 
 
-def hipref_step(Td_old: np.ndarray, r: float, nx: int, ny: int, ng: int = 1) -> np.ndarray:
+def hipref_step(Td_old: np.ndarray, r: float, nx: int, ny: int, ng: int = 1, contract: bool = False) -> np.ndarray:
     """One launch_heat_eqn (fortran/hip/heat_kernel.cpp:48-61) on a ghosted [(ny+2ng), (nx+2ng)]
-    array, preceded by the Td_old = Td copy of fortran/hip/heat.F90:243."""
-    L = _load("_ref/libhipref.so")
+    array, preceded by the Td_old = Td copy of fortran/hip/heat.F90:243.  ``contract``: the host build
+    with FMA contraction on (what hipcc's default -ffp-contract=fast does to the same text)."""
+    L = _load("_ref/libhipref_fma.so" if contract else "_ref/libhipref.so")
     L.launch_heat_eqn.argtypes = [_dp, _dp, C.c_double, C.c_int, C.c_int, C.c_int]
     L.launch_heat_eqn.restype = None
     old = np.ascontiguousarray(Td_old, dtype=np.float64)
@@ -109,9 +121,10 @@ def hipref_recv(Td: np.ndarray, Tdr: np.ndarray, which: int, nx: int, ny: int, n
     return a
 
 
-def pycudaref_step(u_old: np.ndarray, r: float) -> np.ndarray:
-    """One heatCalculate launch as python/cuda/cuda.py:97-99 issues it (u_new starts as u_old)."""
-    L = _load("_ref/libpycudaref.so")
+def pycudaref_step(u_old: np.ndarray, r: float, contract: bool = False) -> np.ndarray:
+    """One heatCalculate launch as python/cuda/cuda.py:97-99 issues it (u_new starts as u_old).
+    ``contract``: the host build with FMA contraction on (nvcc's default -fmad=true)."""
+    L = _load("_ref/libpycudaref_fma.so" if contract else "_ref/libpycudaref.so")
     L.pycuda_ref_launch.argtypes = [_dp, _dp, C.c_int, C.c_int, C.c_double]
     old = np.ascontiguousarray(u_old, dtype=np.float64)
     ny, nx = old.shape

@@ -18,14 +18,28 @@
 #include <string.h>
 #include <stdlib.h>
 
+/* Contracted evaluation (contract != 0), orders 0 and 1 only: what the reference's own GPU toolchains make
+ * of the same source text — nvcc (-fmad=true by default, PyCUDA SourceModule, python/cuda/cuda.py:86) and
+ * hipcc (-ffp-contract=fast, fortran/hip/Makefile) fuse  c + r*(t - 4*c)  into  fma(r, fma(-4, c, t), c).
+ * Pinned against oracle/_ref/lib*ref_fma.so = the reference kernels compiled with gcc -mfma
+ * -ffp-contract=fast (the _fma arrays under tests/golden/). */
+#define FMA_double(a, b, c) __builtin_fma((a), (b), (c))
+#define FMA_float(a, b, c) __builtin_fmaf((a), (b), (c))
+
 #define DEFINE_STEP(T, SUF)                                                                       \
     static void step_##SUF(T *restrict dst, const T *restrict src, int nx, int ny, size_t pitch,  \
-                           T rx, T ry, int order) {                                               \
+                           T rx, T ry, int order, int contract) {                                 \
         _Pragma("omp parallel for schedule(static)")                                              \
         for (int y = 1; y < ny - 1; ++y) {                                                        \
             const T *c = src + (size_t)y * pitch, *n = c + pitch, *s = c - pitch;                 \
             T *o = dst + (size_t)y * pitch;                                                       \
-            if (order == 0) {                                                                     \
+            if (contract) {                                                                       \
+                for (int x = 1; x < nx - 1; ++x) {                                                \
+                    T t = order == 0 ? ((c[x + 1] + n[x]) + c[x - 1]) + s[x]                      \
+                                     : ((c[x - 1] + c[x + 1]) + n[x]) + s[x];                     \
+                    o[x] = FMA_##T(rx, FMA_##T((T)-4, c[x], t), c[x]);                            \
+                }                                                                                 \
+            } else if (order == 0) {                                                                     \
                 for (int x = 1; x < nx - 1; ++x)                                                  \
                     o[x] = c[x] + rx * ((((c[x + 1] + n[x]) + c[x - 1]) + s[x]) - (T)4 * c[x]);   \
             } else if (order == 1) {                                                              \
@@ -39,23 +53,41 @@
         }                                                                                         \
     }                                                                                             \
     /* steps Jacobi steps in place on u; returns 0, or -1 on bad arguments / no memory. */        \
-    int oracle_march_##SUF(T *u, int nx, int ny, size_t pitch, T rx, T ry, int order,             \
-                           int steps) {                                                           \
+    int oracle_march_ex_##SUF(T *u, int nx, int ny, size_t pitch, T rx, T ry, int order,          \
+                              int steps, int contract) {                                          \
         if (!u || nx < 1 || ny < 1 || pitch < (size_t)nx || order < 0 || order > 2) return -1;    \
+        if (contract && order == 2) return -1;   /* NumPy never contracts (heat.py:50-54) */      \
         if (steps <= 0 || nx < 3 || ny < 3) return 0;                                             \
         size_t bytes = (size_t)ny * pitch * sizeof(T);                                            \
         T *old = (T *)malloc(bytes);                                                              \
         if (!old) return -1;                                                                      \
         for (int t = 0; t < steps; ++t) {                                                         \
             memcpy(old, u, bytes);             /* T_old = T   (heat.f90:63, heat.py:49) */        \
-            step_##SUF(u, old, nx, ny, pitch, rx, ry, order);                                     \
+            step_##SUF(u, old, nx, ny, pitch, rx, ry, order, contract);                           \
         }                                                                                         \
         free(old);                                                                                \
         return 0;                                                                                 \
+    }                                                                                             \
+    int oracle_march_##SUF(T *u, int nx, int ny, size_t pitch, T rx, T ry, int order,             \
+                           int steps) {                                                           \
+        return oracle_march_ex_##SUF(u, nx, ny, pitch, rx, ry, order, steps, 0);                  \
     }
 
 DEFINE_STEP(double, f64)
 DEFINE_STEP(float, f32)
+
+/* Threads the OpenMP build will use for a march (1 in the serial build); n > 0 sets the count first.
+ * bench.py calls it so that the CPU arm's thread count is explicit and reported, whatever
+ * OMP_NUM_THREADS the launcher exported. */
+#ifdef _OPENMP
+#include <omp.h>
+int oracle_threads(int n) {
+    if (n > 0) omp_set_num_threads(n);
+    return omp_get_max_threads();
+}
+#else
+int oracle_threads(int n) { (void)n; return 1; }
+#endif
 
 /* delta, dt, r of fortran/serial/heat.f90:15,17,59. */
 void oracle_derive_fortran(int n, double sigma, double nu, double dom_len, double *delta,

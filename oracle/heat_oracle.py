@@ -10,7 +10,11 @@ Parity pinning: the reference ships no tests or golden vectors. 
 is pinned instead against outputs of the reference itself, produced in the build container:
 ``python/serial/heat.py`` executed unmodified (``oracle/run_reference.py``), the reference's
 HIP kernel source and PyCUDA kernel string compiled for the host (``oracle/_ref``), all
-frozen as fixtures under ``tests/golden/`` by ``tests/golden/make_golden.py``.
+frozen as fixtures under ``tests/golden/`` by ``tests/golden/make_golden.py``.  Order P is pinned by
+the script's own ``diffuse(60)`` (61 steps past its shipped run: rounding-sensitive, so it tells
+order P from F and C); orders F and C by random fields through the host-compiled kernels — in their
+uncontracted reading (gcc -ffp-contract=off) here, and in the contracted reading that nvcc / hipcc
+give the same text by default in oracle/heat_oracle.c (``contract``), which NumPy cannot express.
 
 Every function cites the reference file:line it follows (paths relative to the reference root).
 Array convention everywhere: ``u[y, x]`` C-order, x contiguous — the same bytes as the Fortran
@@ -165,6 +169,20 @@ def pyserial_diffuse(nx=31, ny=31, nt=10, nu=.05, sigma=.25, length=2):
     _, _, _, cx, cy = derive_python(nx, ny, nu, sigma, length)
     u = ic_pyserial(nx, ny, length)
     return march(u, nt + 1, ORDER_PYSERIAL, cx, cy)
+
+
+def pyserial_diffuse_calls(calls, nx=31, ny=31, nu=.05, sigma=.25, length=2, march_fn=None):
+    """The module body of python/serial/heat.py followed by ``diffuse(nt)`` for every nt in ``calls``, the
+    way the script's own function behaves when called again (heat.py:45-48): each call writes the hat
+    value 2 back into the CURRENT field's hat slice and then runs nt + 1 steps."""
+    dx, dy, _, cx, cy = derive_python(nx, ny, nu, sigma, length)
+    u = ic_pyserial(nx, ny, length)
+    march_fn = march if march_fn is None else march_fn
+    for nt in calls:
+        u = np.array(u, copy=True)
+        u[int(.5 / dy):int(1 / dy + 1), int(.5 / dx):int(1 / dx + 1)] = 2      # heat.py:46
+        u = march_fn(u, nt + 1, ORDER_PYSERIAL, cx, cy)
+    return u
 
 
 def fortran_serial(n, sigma, nu, dom_len, ntime, y_hi=1.5):

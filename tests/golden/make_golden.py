@@ -12,6 +12,14 @@ Sources of truth, none of them ours:
                         (oracle/_ref/libpycudaref.so), 5 launches on a seeded 64x64 field, for
                         r = 0.25 and for r = 0.24999999999999997 (n = 100)
 
+  pyserial_31_diffuse60.npz   the same unmodified script, then ITS OWN diffuse(60) called from the
+                        script's globals (heat.py:45-58: hat re-applied to the diffused field,
+                        61 more steps) — far outside the exact-arithmetic window, so the bits
+                        depend on operation order P
+  *_fma arrays          the same reference kernel sources compiled with gcc -mfma
+                        -ffp-contract=fast (oracle/_ref/lib*ref_fma.so): the contracted reading
+                        nvcc (-fmad=true) and hipcc (-ffp-contract=fast) give that text by default
+
 Run:  python tests/golden/make_golden.py
 """
 import os
@@ -31,6 +39,14 @@ def golden_pyserial():
     np.savez_compressed(os.path.join(OUT, "pyserial_31.npz"), u=g["u"], nx=g["nx"], ny=g["ny"],
                         nt_called=10, dx=g["dx"], dy=g["dy"], dt=g["dt"], nu=g["nu"], sigma=g["sigma"])
     print("pyserial_31: sum", repr(float(g["u"].sum())))
+
+
+def golden_pyserial_diffuse60():
+    g = run_reference.run_python_serial()       # module body + diffuse(10), as shipped
+    u10 = g["u"].copy()
+    g["diffuse"](60)                            # the reference's own function, heat.py:45-58
+    np.savez_compressed(os.path.join(OUT, "pyserial_31_diffuse60.npz"), u10=u10, u=g["u"], calls=np.array([10, 60]))
+    print("pyserial_31_diffuse60: sum", repr(float(g["u"].sum())))
 
 
 def hip_program(n, nproc, ntime, dom_len=2.0, sigma=0.25, nu=0.05):
@@ -63,6 +79,10 @@ def golden_hip():
     for _ in range(5):
         g = c_oracle.hipref_step(g, out["r"], 56, 40, 1)
     out["rand_u0"], out["rand_u5"] = g0, g
+    g = g0
+    for _ in range(5):
+        g = c_oracle.hipref_step(g, out["r"], 56, 40, 1, contract=True)
+    out["rand_u5_fma"] = g
     np.savez_compressed(os.path.join(OUT, "hip_slabs_n100.npz"), **out)
     print("hip_slabs_n100: r", repr(out["r"]), "sum P1", repr(float(out["P1_rank0"].sum())))
 
@@ -78,6 +98,10 @@ def golden_pycuda():
             u = c_oracle.pycudaref_step(u, r)
         out["r_" + tag] = r
         out["u5_" + tag] = u
+        u = u0
+        for _ in range(5):
+            u = c_oracle.pycudaref_step(u, r, contract=True)
+        out["u5_" + tag + "_fma"] = u
     np.savez_compressed(os.path.join(OUT, "pycuda_kernel.npz"), **out)
     print("pycuda_kernel: sum", repr(float(out["u5_rn100"].sum())))
 
@@ -87,5 +111,6 @@ if __name__ == "__main__":
         sys.exit("reference tree not found; fixtures can only be regenerated in the build container")
     c_oracle.build(ref=True)
     golden_pyserial()
+    golden_pyserial_diffuse60()
     golden_hip()
     golden_pycuda()

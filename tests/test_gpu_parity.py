@@ -39,6 +39,29 @@ def test_pyserial_dropin_matches_reference_run(golden):
     assert float(serial.u.sum()) == 1041.943124294281
 
 
+@pytest.mark.parametrize("kernel", ["auto", "simple", "stream", "tma", "wtma"])
+def test_pyserial_dropin_rounding_sensitive_reference_run(golden, kernel):
+    """The reference script followed by ITS OWN diffuse(60) (tests/golden/make_golden.py): 72 steps, past the
+    exact-arithmetic window, so only op order P (heat.py:50-54) reproduces these bits."""
+    from heatb200 import serial
+    g = golden("pyserial_31_diffuse60.npz")
+    serial.configure(n=31)
+    serial.kernel = kernel
+    try:
+        serial.diffuse(10)
+        assert_bit_equal(serial.u, g["u10"])
+        serial.diffuse(60)
+        assert_bit_equal(serial.u, g["u"])
+    finally:
+        serial.kernel = "auto"
+    # the same input through order F is close but not bit-equal: the golden does discriminate
+    dx, dy = serial.dx, serial.dy
+    v = g["u10"].copy()
+    v[int(.5 / dy):int(1 / dy + 1), int(.5 / dx):int(1 / dx + 1)] = 2
+    f = heatb200.march(v, 61, 0.25, order="fortran", kernel=kernel)
+    assert not np.array_equal(bits(f), bits(g["u"])) and np.abs(f - g["u"]).max() < 1e-14
+
+
 @pytest.mark.parametrize("kernel", KERNELS + ["resident", "auto"])
 def test_pyserial_case_every_kernel(golden, kernel):
     u0 = ic.hat_pyserial(31, 31)
@@ -64,6 +87,28 @@ def test_pycuda_kernel_goldens(golden, kernel, tag):
     g = golden("pycuda_kernel.npz")
     got = heatb200.march(g["u0"], 5, float(g["r_" + tag]), order="pycuda", kernel=kernel)
     assert_bit_equal(got, g["u5_" + tag])
+
+
+@pytest.mark.parametrize("kernel", KERNELS + ["resident"])
+def test_contracted_goldens_bit_exact_with_fmad(golden, kernel):
+    """HEAT_FLAG_FMAD + orders C / F = the reference's GPU kernel text as nvcc (-fmad=true) / hipcc
+    (-ffp-contract=fast) compile it by default: bit-equal to the reference sources built for the host with
+    contraction on (the *_fma goldens), and to the C oracle's contracted mode on other shapes."""
+    p = golden("pycuda_kernel.npz")
+    for tag in ("r025", "rn100"):
+        got = heatb200.march(p["u0"], 5, float(p["r_" + tag]), order="pycuda", kernel=kernel, fmad=True)
+        assert_bit_equal(got, p["u5_" + tag + "_fma"])
+    h = golden("hip_slabs_n100.npz")
+    got = heatb200.march(h["rand_u0"], 5, float(h["r"]), order="fortran", kernel=kernel, fmad=True)
+    assert_bit_equal(got, h["rand_u5_fma"])
+    if kernel != "resident":
+        for dtype in (np.float64, np.float32):
+            u0 = rand_field((130, 257), dtype, seed=12)
+            for order in ("fortran", "pycuda"):
+                want = c_oracle.march(u0, 9, ho.ORDERS[order], dtype(R100), contract=True)
+                assert_bit_equal(heatb200.march(u0, 9, float(dtype(R100)), order=order, kernel=kernel, fmad=True), want)
+                for k in (2, 4):
+                    assert_bit_equal(heatb200.march(u0, 9, float(dtype(R100)), order=order, kernel="tma", tblock=k, fmad=True), want)
 
 
 # ------------------------------------------------------------------ oracle, seeded inputs, ragged shapes
@@ -348,6 +393,48 @@ def test_legacy_launcher_large_ghosted_array():
     heatb200.lib().launch_heat_eqn(C.c_void_p(new.data_ptr()), C.c_void_p(old.data_ptr()), R100, nx, ny, ng)
     torch.cuda.synchronize()
     assert_bit_equal(new.cpu().numpy(), ho.march(g0, 1, ho.ORDER_FORTRAN, R100))
+
+
+def test_legacy_launcher_contracted_and_single_precision(golden):
+    """heat_legacy_set_fmad(1): launch_heat_eqn fuses as hipcc's default does -> the contracted hip golden;
+    launch_*_sp: the -DSINGLE_PRECISION flavour of the reference's `real` (heat_kernel.cpp:5-9)."""
+    import ctypes as C
+    import torch
+    L = heatb200.lib()
+    h = golden("hip_slabs_n100.npz")
+    r, nx, ny, ng = float(h["r"]), 56, 40, 1
+    p = lambda t: C.c_void_p(t.data_ptr())
+    for fm, key in ((1, "rand_u5_fma"), (0, "rand_u5")):
+        prev = L.heat_legacy_set_fmad(fm)
+        try:
+            cur = torch.from_numpy(h["rand_u0"]).cuda()
+            for _ in range(5):
+                old = cur.clone()
+                L.launch_heat_eqn(p(cur), p(old), r, nx, ny, ng)
+            torch.cuda.synchronize()
+        finally:
+            L.heat_legacy_set_fmad(prev)
+        assert_bit_equal(cur.cpu().numpy(), h[key])
+    assert L.heat_legacy_set_fmad(0) == 0
+    # fp32 flavour: update on small (thread-per-cell) and large (row-marching) ghosted arrays, then pack/unpack
+    for nx, ny in ((56, 40), (1000, 300)):
+        g0 = rand_field((ny + 2, nx + 2), np.float32, seed=nx)
+        old = torch.from_numpy(g0).cuda()
+        new = old.clone()
+        L.launch_heat_eqn_sp(p(new), p(old), np.float32(R100), nx, ny, ng)
+        torch.cuda.synchronize()
+        assert_bit_equal(new.cpu().numpy(), ho.march(g0, 1, ho.ORDER_FORTRAN, np.float32(R100)))
+        s1 = torch.zeros(ng * ny, dtype=torch.float32, device="cuda")
+        s2 = torch.zeros_like(s1)
+        L.launch_send_sp(p(new), p(s1), p(s2), nx, ny, ng)
+        torch.cuda.synchronize()
+        got = new.cpu().numpy()
+        assert np.array_equal(s1.cpu().numpy(), got[1:-1, 1]) and np.array_equal(s2.cpu().numpy(), got[1:-1, nx])
+        L.launch_recv1_sp(p(new), p(s2), nx, ny, ng)
+        L.launch_recv2_sp(p(new), p(s1), nx, ny, ng)
+        torch.cuda.synchronize()
+        after = new.cpu().numpy()
+        assert np.array_equal(after[1:-1, 0], got[1:-1, nx]) and np.array_equal(after[1:-1, nx + 1], got[1:-1, 1])
 
 
 def test_legacy_hip_abi(golden):

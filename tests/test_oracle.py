@@ -41,7 +41,30 @@ def test_pyserial_params(golden):
 
 @pytest.mark.skipif(not run_reference.available(), reason="reference tree only in the build container")
 def test_reference_run_matches_committed_golden(golden):
-    assert_bit_equal(run_reference.run_python_serial()["u"], golden("pyserial_31.npz")["u"])
+    g = run_reference.run_python_serial()
+    assert_bit_equal(g["u"], golden("pyserial_31.npz")["u"])
+    g["diffuse"](60)                                   # the reference's own function, heat.py:45-58
+    assert_bit_equal(g["u"], golden("pyserial_31_diffuse60.npz")["u"])
+
+
+def test_order_p_pinned_by_rounding_sensitive_reference_run(golden):
+    """pyserial_31_diffuse60.npz = the unmodified script, then its own diffuse(60): 72 steps in all, far past
+    the ~26-step exact-arithmetic window, so the three op orders give DIFFERENT bits and only order P
+    (heat.py:50-54) reproduces the reference."""
+    g = golden("pyserial_31_diffuse60.npz")
+    assert_bit_equal(g["u10"], golden("pyserial_31.npz")["u"])
+    want = g["u"]
+    assert_bit_equal(ho.pyserial_diffuse_calls([10, 60]), want)
+    assert_bit_equal(ho.pyserial_diffuse_calls([10, 60], march_fn=c_oracle.march), want)
+    # the same input through orders F and C: close, but not the reference's bits
+    dx, dy, _, cx, cy = ho.derive_python(31, 31)
+    v = g["u10"].copy()
+    v[int(.5 / dy):int(1 / dy + 1), int(.5 / dx):int(1 / dx + 1)] = 2
+    assert_bit_equal(ho.march(v, 61, ho.ORDER_PYSERIAL, cx, cy), want)
+    for order in (ho.ORDER_FORTRAN, ho.ORDER_PYCUDA):
+        other = ho.march(v, 61, order, cx, cy)
+        assert not np.array_equal(bits(other), bits(want))
+        assert np.abs(other - want).max() < 1e-14
 
 
 # ----------------------------------------------------------------- HIP kernels (reference source on host)
@@ -80,6 +103,27 @@ def test_oracles_match_pycuda_kernel(golden, tag):
     assert_bit_equal(c_oracle.march(g["u0"], 5, ho.ORDER_PYCUDA, r), g["u5_" + tag])
 
 
+def test_contracted_reading_of_gpu_kernels(golden):
+    """nvcc (-fmad=true, PyCUDA's default) and hipcc (-ffp-contract=fast) fuse c + r*(t - 4c) into
+    fma(r, fma(-4, c, t), c).  The *_fma goldens are the reference kernel sources compiled for the host
+    with contraction on; the C oracle's `contract` mode must reproduce them, and they must differ from
+    the uncontracted goldens exactly when r is not a power of two."""
+    h = golden("hip_slabs_n100.npz")
+    r = float(h["r"])
+    assert_bit_equal(c_oracle.march(h["rand_u0"], 5, ho.ORDER_FORTRAN, r, contract=True), h["rand_u5_fma"])
+    assert not np.array_equal(bits(h["rand_u5_fma"]), bits(h["rand_u5"]))
+    assert np.max(np.abs(h["rand_u5_fma"] - h["rand_u5"]) / h["rand_u5"]) <= 1e-12
+    p = golden("pycuda_kernel.npz")
+    for tag, differs in (("r025", False), ("rn100", True)):
+        rr = float(p["r_" + tag])
+        assert_bit_equal(c_oracle.march(p["u0"], 5, ho.ORDER_PYCUDA, rr, contract=True), p["u5_" + tag + "_fma"])
+        assert (not np.array_equal(bits(p["u5_" + tag + "_fma"]), bits(p["u5_" + tag]))) == differs
+    u32 = p["u0"].astype(np.float32)
+    a = c_oracle.march(u32, 5, ho.ORDER_PYCUDA, np.float32(0.2437), contract=True)
+    b = c_oracle.march(u32, 5, ho.ORDER_PYCUDA, np.float32(0.2437))
+    assert a.dtype == np.float32 and np.max(np.abs(a - b) / b) <= 1e-5
+
+
 def test_pycuda_ic_is_uniform():
     """python/cuda/cuda.py:53 — empty slice; the shipped run is a fixed point."""
     u = ho.ic_pycuda(128, 128)
@@ -99,6 +143,12 @@ def test_ref_builds_match_goldens(golden):
     for _ in range(5):
         v = c_oracle.hipref_step(v, float(h["r"]), 56, 40, 1)
     assert_bit_equal(v, h["rand_u5"])
+    u, v = g["u0"], h["rand_u0"]
+    for _ in range(5):
+        u = c_oracle.pycudaref_step(u, float(g["r_rn100"]), contract=True)
+        v = c_oracle.hipref_step(v, float(h["r"]), 56, 40, 1, contract=True)
+    assert_bit_equal(u, g["u5_rn100_fma"])
+    assert_bit_equal(v, h["rand_u5_fma"])
 
 
 # ----------------------------------------------------------------- C vs NumPy restatements
