@@ -17,6 +17,7 @@
 #include "kernels_basic.cuh"
 #include "kernels_tma.cuh"
 #include "kernels_temporal.cuh"
+#include "kernels_persist.cuh"
 #include "nccl_dyn.h"
 
 using namespace heat;
@@ -54,8 +55,14 @@ static int fail(int code, const char* fmt, ...) {
 struct heat_handle {
     heat_config cfg{};
     int dev = 0;
-    int nx = 0, ny = 0;            // global
+    int nx = 0;                    // LOCAL width: what the kernels see (own columns + ghost columns); == gnx for row slabs
+    int gnx = 0, ny = 0;           // global
     int row0 = 0, nrows = 0;       // owned global rows
+    // 2-D (px x py) decomposition: rank = ry * px + rx.  Row slabs are px == 1.
+    int px = 1, py = 1, rxi = 0, ryi = 0;
+    int col0 = 0, ncols = 0;       // owned global columns
+    int gl = 0, gr = 0;            // ghost columns held on the left / right (g next to a neighbour, 0 at the domain's edge)
+    void* colbuf[4] = {nullptr, nullptr, nullptr, nullptr};   // packed column halos: send left, send right, recv left, recv right
     int g = 0;                     // ghost depth (0 when nranks == 1)
     int lrows = 0;                 // nrows + 2g
     long pitch = 0;                // elements
@@ -79,6 +86,13 @@ struct heat_handle {
     double* d_sum = nullptr;
     void* d_stage = nullptr;       // global-gather staging on the root (lazily allocated)
     size_t stage_bytes = 0;
+    // job pipeline (heat_submit / heat_drain): device staging for the next job's input and the previous job's
+    // result, moved over PCIe on their own streams while the current job marches
+    void* pipe_in = nullptr;
+    void* pipe_out = nullptr;
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaEvent_t ev_up = nullptr, ev_in_free = nullptr, ev_res = nullptr, ev_out_free = nullptr;
+    uint64_t pipe_jobs = 0;
     TmaState tma;                  // tensor maps for the TMA kernels (kernels_tma.cuh)
     TemporalState temporal;        // tensor maps for the fused K-step kernel (kernels_temporal.cuh)
     // peer-memory halo (HEAT_FLAG_PEER_HALO): neighbours' buffers and flag words mapped through CUDA IPC
@@ -93,6 +107,11 @@ struct heat_handle {
     int sm_count = 148;
     int stream_rows = 0, stream_threads = 0;   // tuning overrides (env)
     uint64_t steps_total = 0, launches = 0, exchanges = 0;
+    PersistPlan persist;           // on-chip persistent stepping (kernels_persist.cuh): slabs, ghost depth, smem
+    void* p_mailbox = nullptr;     // its neighbour mailbox (global scratch) and per-slab epoch flags
+    unsigned* p_flags = nullptr;
+    unsigned p_epoch = 0;
+    int persist_min_nt = 8;        // shorter heat_step calls are not worth loading the field on chip
     void* mirror_base = nullptr;   // transient: second destination (peer ghost rows) of the next update launch
     int mirror_shift = 0;
     int kflags = 0;                // KF_* of the next launches: sweep direction (alternates per advance) + L2 policy
@@ -140,7 +159,7 @@ static cudaError_t launch_rows_t(heat_handle* h, const void* src, void* dst, int
         const int ybc0 = h->g - h->row0, ybc1 = h->ny - 1 - h->row0 + h->g;
         return launch_temporal_rows<T, ORDER, FMA, 1>(h->temporal, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch, yb, ye,
                                                      ybc0, ybc1, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
-    } else if (h->kernel == HEAT_KERNEL_TMA) {
+    } else if (h->kernel == HEAT_KERNEL_TMA || h->kernel == HEAT_KERNEL_PERSIST) {
         return launch_tma_rows<T, ORDER, FMA>(h->tma, src == h->buf[0] ? 0 : 1, D, h->nx, h->pitch,
                                               yb, ye, rx, ry, h->sm_count, s, h->kflags, (T*)h->mirror_base, h->mirror_shift);
     } else {
@@ -162,6 +181,28 @@ static cudaError_t launch_resident_t(heat_handle* h, const void* src, void* dst,
     h->launches++;
     k<<<1, threads, smem, s>>>((const T*)src, (T*)dst, h->nx, h->ny, h->pitch, nt, (T)h->cfg.rx, (T)h->cfg.ry);
     return cudaGetLastError();
+}
+
+template <typename T, int ORDER, bool FMA>
+static cudaError_t launch_persist_t(heat_handle* h, const void* src, void* dst, int nt, cudaStream_t s) {
+    auto k = heat_persist_kernel<T, ORDER, FMA>;
+    // the attribute is set once per kernel and device, so ask for the most any plan can need
+    int smem_cap = 0;
+    cudaDeviceGetAttribute(&smem_cap, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->dev);
+    cudaError_t e = ensure_dynamic_smem<heat_persist_kernel<T, ORDER, FMA>>((size_t)smem_cap);
+    if (e != cudaSuccess) return e;
+    const T* S = (const T*)src;
+    T* D = (T*)dst;
+    int nx = h->nx, ny = h->ny, G = h->persist.G, spitch = h->persist.spitch, lmax = h->persist.lmax;
+    long pitch = h->pitch;
+    T rx = (T)h->cfg.rx, ry = (T)h->cfg.ry;
+    T* mailbox = (T*)h->p_mailbox;
+    unsigned* flags = h->p_flags;
+    unsigned epoch0 = h->p_epoch;
+    void* args[] = {&S, &D, &nx, &ny, &pitch, &nt, &G, &spitch, &lmax, &rx, &ry, &mailbox, &flags, &epoch0};
+    h->launches++;
+    h->p_epoch += (unsigned)((nt + G - 1) / G);      // one epoch per neighbour exchange, an upper bound is enough
+    return cudaLaunchCooperativeKernel((const void*)k, dim3(h->persist.P), dim3(kPersistThreads), args, h->persist.smem, s);
 }
 
 template <typename T, int ORDER, bool FMA>
@@ -287,6 +328,36 @@ static int exchange_peer(heat_handle* h, int which, cudaStream_t s) {
     return HEAT_OK;
 }
 
+// Column halos of the 2-D decomposition are strided (g cells out of every row), so they travel packed:
+// one kernel gathers both edge blocks into [rows][g] buffers (pack = 1) or scatters the received blocks into the
+// ghost columns (pack = 0).  ref: the reference's own strided direction, pack -> sendrecv -> unpack,
+// fortran/mpi+cuda/heat.F90:153-159,175-190.
+template <typename T>
+__global__ void __launch_bounds__(256)
+heat_cols_kernel(T* __restrict__ field, long pitch, int rows, int g, int c_left, int c_right, T* __restrict__ bleft,
+                 T* __restrict__ bright, int pack) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long)rows * g) return;
+    const long r = i / g;
+    const int j = (int)(i % g);
+    T* row = field + r * pitch;
+    if (pack) {
+        if (bleft) bleft[i] = row[c_left + j];
+        if (bright) bright[i] = row[c_right + j];
+    } else {
+        if (bleft) row[c_left + j] = bleft[i];
+        if (bright) row[c_right + j] = bright[i];
+    }
+}
+
+template <typename T>
+static cudaError_t launch_cols(heat_handle* h, int which, int c_left, int c_right, void* bl, void* br, int pack, cudaStream_t s) {
+    const long n = (long)h->lrows * h->g;
+    heat_cols_kernel<T><<<(unsigned)((n + 255) / 256), 256, 0, s>>>((T*)h->buf[which], h->pitch, h->lrows, h->g, c_left, c_right,
+                                                                    (T*)bl, (T*)br, pack);
+    return cudaGetLastError();
+}
+
 static int exchange(heat_handle* h, int which, cudaStream_t s) {
     if (h->cfg.nranks <= 1) return HEAT_OK;
     h->exchanges++;
@@ -298,22 +369,54 @@ static int exchange(heat_handle* h, int which, cudaStream_t s) {
     const NcclApi& N = nccl_api();
     const size_t count = (size_t)h->g * h->pitch;
     const int dt = h->cfg.dtype == HEAT_F32 ? ncclFloat32 : ncclFloat64;
-    const int up = h->cfg.rank - 1, down = h->cfg.rank + 1;
+    // rank = ry * px + rx: the rank above / below is px away (row slabs: px == 1)
+    const int up = h->ryi > 0 ? h->cfg.rank - h->px : -1, down = h->ryi + 1 < h->py ? h->cfg.rank + h->px : -1;
     CUDA_TRY(cudaEventRecord(h->ev_h0, s));
-    NCCL_TRY(N.GroupStart());
-    ncclResult_t gr = 0;                       // first failure inside the group; the group is closed regardless
+    ncclResult_t gr = 0;                       // first failure inside a group; the group is closed regardless
     auto in_group = [&](ncclResult_t r) { if (gr == 0) gr = r; };
-    if (up >= 0) {
-        in_group(N.Send(row_ptr(h, which, h->g), count, dt, up, h->comm, s));
-        in_group(N.Recv(row_ptr(h, which, 0), count, dt, up, h->comm, s));
+    if (h->py > 1) {
+        // phase 1: g full local rows up and down (with px > 1 they include the ghost columns, whose corner blocks
+        // are put right by phase 2)
+        NCCL_TRY(N.GroupStart());
+        if (up >= 0) {
+            in_group(N.Send(row_ptr(h, which, h->g), count, dt, up, h->comm, s));
+            in_group(N.Recv(row_ptr(h, which, 0), count, dt, up, h->comm, s));
+        }
+        if (down >= 0) {
+            in_group(N.Send(row_ptr(h, which, h->nrows), count, dt, down, h->comm, s));
+            in_group(N.Recv(row_ptr(h, which, h->g + h->nrows), count, dt, down, h->comm, s));
+        }
+        const ncclResult_t ge = N.GroupEnd();
+        if (gr != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclSend/ncclRecv failed: %s", N.GetErrorString(gr));
+        if (ge != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclGroupEnd failed: %s", N.GetErrorString(ge));
     }
-    if (down < h->cfg.nranks) {
-        in_group(N.Send(row_ptr(h, which, h->nrows), count, dt, down, h->comm, s));
-        in_group(N.Recv(row_ptr(h, which, h->g + h->nrows), count, dt, down, h->comm, s));
+    if (h->px > 1) {
+        // phase 2: g own columns left and right over ALL local rows — ghost rows included, which is what carries the
+        // diagonal neighbours' cells into the corner blocks (needed as soon as g > 1)
+        const int left = h->rxi > 0 ? h->cfg.rank - 1 : -1, right = h->rxi + 1 < h->px ? h->cfg.rank + 1 : -1;
+        const size_t ccount = (size_t)h->lrows * h->g;
+        void* sl = left >= 0 ? h->colbuf[0] : nullptr;
+        void* sr = right >= 0 ? h->colbuf[1] : nullptr;
+        void* rl = left >= 0 ? h->colbuf[2] : nullptr;
+        void* rr = right >= 0 ? h->colbuf[3] : nullptr;
+        const int own_first = h->gl, own_last = h->gl + h->ncols - h->g;        // first / last g own columns
+        CUDA_TRY(h->cfg.dtype == HEAT_F32 ? launch_cols<float>(h, which, own_first, own_last, sl, sr, 1, s)
+                                          : launch_cols<double>(h, which, own_first, own_last, sl, sr, 1, s));
+        NCCL_TRY(N.GroupStart());
+        if (left >= 0) {
+            in_group(N.Send(sl, ccount, dt, left, h->comm, s));
+            in_group(N.Recv(rl, ccount, dt, left, h->comm, s));
+        }
+        if (right >= 0) {
+            in_group(N.Send(sr, ccount, dt, right, h->comm, s));
+            in_group(N.Recv(rr, ccount, dt, right, h->comm, s));
+        }
+        const ncclResult_t ge = N.GroupEnd();
+        if (gr != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclSend/ncclRecv (columns) failed: %s", N.GetErrorString(gr));
+        if (ge != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclGroupEnd (columns) failed: %s", N.GetErrorString(ge));
+        CUDA_TRY(h->cfg.dtype == HEAT_F32 ? launch_cols<float>(h, which, 0, h->gl + h->ncols, rl, rr, 0, s)
+                                          : launch_cols<double>(h, which, 0, h->gl + h->ncols, rl, rr, 0, s));
     }
-    const ncclResult_t ge = N.GroupEnd();
-    if (gr != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclSend/ncclRecv failed: %s", N.GetErrorString(gr));
-    if (ge != 0) return fail(HEAT_ERR_NCCL, "halo exchange: ncclGroupEnd failed: %s", N.GetErrorString(ge));
     CUDA_TRY(cudaEventRecord(h->ev_h1, s));
     h->halo_timed = true;
     return HEAT_OK;
@@ -347,17 +450,28 @@ static int resolve_kernel(heat_handle* h) {
     const bool fits_resident = c.nranks == 1 && h->nx >= 3 && h->ny >= 3 &&
                                2 * (size_t)h->nx * h->ny * h->esize <= 200 * 1024;
     h->vec_ok = aligned;
+    int smem_cap = 0;
+    cudaDeviceGetAttribute(&smem_cap, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->dev);
+    if (c.nranks == 1 && aligned && h->tblock == 1)
+        h->persist = persist_plan(h->nx, h->ny, h->esize, h->sm_count, (size_t)std::max(0, smem_cap - 1024));
+    const bool fits_persist = h->persist.ok;
     int k = c.kernel;
     if (k == HEAT_KERNEL_AUTO) {
         if (fits_resident) k = HEAT_KERNEL_RESIDENT;
+        // the whole field fits in the SMs' shared memory: one launch for all steps.  Measured (tools/bench_small.py)
+        // it beats per-step launches while a ghost depth >= 3 fits (fp64 up to 1024^2), not beyond (1100^2: G = 2)
+        else if (fits_persist && h->persist.G >= 3) k = HEAT_KERNEL_PERSIST;
         else if (aligned) k = HEAT_KERNEL_TMA;       // measured fastest for fp64 and fp32 at 4096^2 and 16384^2 (profiles/)
         else k = HEAT_KERNEL_STREAM;                 // its one-cell-per-lane variant needs no alignment
     }
     if (k == HEAT_KERNEL_RESIDENT && !fits_resident)
         return fail(HEAT_ERR_UNSUPPORTED, "RESIDENT kernel needs nranks == 1 and 2*nx*ny*sizeof(T) <= 200 KiB");
+    if (k == HEAT_KERNEL_PERSIST && !fits_persist)
+        return fail(HEAT_ERR_UNSUPPORTED, "PERSIST kernel needs nranks == 1, tblock == 1, 16-byte friendly buffers and a field whose row slabs "
+                                          "(two copies, with ghost rows) fit in the SMs' shared memory");
     if ((k == HEAT_KERNEL_TMA || k == HEAT_KERNEL_WTMA) && !aligned)
         return fail(HEAT_ERR_UNSUPPORTED, "TMA kernels need 16-byte aligned buffers and a pitch that is a multiple of %d elements", (int)V);
-    if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_WTMA) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
+    if (k < HEAT_KERNEL_SIMPLE || k > HEAT_KERNEL_PERSIST) return fail(HEAT_ERR_INVALID, "unknown kernel %d", k);
     h->kernel = k;
     return HEAT_OK;
 }
@@ -380,6 +494,14 @@ int heat_slab_partition(int ny, int nranks, int rank, int* row0, int* nrows) {
     *nrows = base + (rank < rem ? 1 : 0);
     *row0 = rank * base + std::min(rank, rem);
     return HEAT_OK;
+}
+
+int heat_tile_partition(int nx, int ny, int ranks_x, int ranks_y, int rank, int* row0, int* nrows, int* col0, int* ncols) {
+    if (ranks_x < 1 || ranks_y < 1 || rank < 0 || rank >= ranks_x * ranks_y || !row0 || !nrows || !col0 || !ncols)
+        return fail(HEAT_ERR_INVALID, "heat_tile_partition: bad arguments (%d x %d ranks, rank %d)", ranks_x, ranks_y, rank);
+    int rc = heat_slab_partition(ny, ranks_y, rank / ranks_x, row0, nrows);
+    if (rc) return rc;
+    return heat_slab_partition(nx, ranks_x, rank % ranks_x, col0, ncols);
 }
 
 int heat_derive_fortran(int n, double sigma, double nu, double dom_len, double* delta, double* dt, double* r) {
@@ -418,11 +540,19 @@ int heat_destroy(heat_handle* h) {
     for (void* p : {h->up_buf[0], h->up_buf[1], h->down_buf[0], h->down_buf[1], (void*)h->up_flags, (void*)h->down_flags})
         if (p) cudaIpcCloseMemHandle(p);
     cudaFree(h->d_flags);
+    cudaFree(h->p_mailbox);
+    cudaFree(h->p_flags);
+    for (void* p : h->colbuf) cudaFree(p);
     if (h->owns) { cudaFree(h->buf[0]); cudaFree(h->buf[1]); }
     cudaFree(h->d_partials);
     cudaFree(h->d_sum);
     cudaFree(h->d_stage);
-    for (cudaEvent_t e : {h->ev_t0, h->ev_t1, h->ev_boundary, h->ev_comm, h->ev_h0, h->ev_h1})
+    for (cudaStream_t st : {h->s_h2d, h->s_d2h})
+        if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    cudaFree(h->pipe_in);
+    cudaFree(h->pipe_out);
+    for (cudaEvent_t e : {h->ev_t0, h->ev_t1, h->ev_boundary, h->ev_comm, h->ev_h0, h->ev_h1, h->ev_up, h->ev_in_free,
+                          h->ev_res, h->ev_out_free})
         if (e) cudaEventDestroy(e);
     if (h->s_comm) cudaStreamDestroy(h->s_comm);
     if (h->owns_stream && h->s_compute) cudaStreamDestroy(h->s_compute);
@@ -430,18 +560,15 @@ int heat_destroy(heat_handle* h) {
     return HEAT_OK;
 }
 
-int heat_set_field(heat_handle* h, const void* src, int64_t src_pitch, int src_is_device) {
-    if (!h || !src) return fail(HEAT_ERR_INVALID, "heat_set_field: null argument");
-    if (src_pitch <= 0) src_pitch = h->nx;
-    if (src_pitch < h->nx) return fail(HEAT_ERR_INVALID, "heat_set_field: src_pitch %lld < nx %d", (long long)src_pitch, h->nx);
-    CUDA_TRY(cudaSetDevice(h->dev));
+// stream-ordered on s_compute, no host synchronisation: `src` becomes this rank's rows of both buffers
+static int install_field(heat_handle* h, const void* src, int64_t src_pitch, int src_is_device) {
     int rc = wait_comm(h);
     if (rc) return rc;
     const cudaMemcpyKind kind = src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     // one trip over PCIe into buffer 0, ONE ghost exchange there (collective), then a device-side copy of
     // own rows and ghost rows into buffer 1 (both buffers need the Dirichlet ring; the ghosts come for free)
-    CUDA_TRY(copy_rows(row_ptr(h, 0, h->g), row_bytes(h), src, (size_t)src_pitch * h->esize,
-                       (size_t)h->nx * h->esize, h->nrows, kind, h->s_compute));
+    CUDA_TRY(copy_rows(row_ptr(h, 0, h->g) + (size_t)h->gl * h->esize, row_bytes(h), src, (size_t)src_pitch * h->esize,
+                       (size_t)h->ncols * h->esize, h->nrows, kind, h->s_compute));
     h->cur = 0;
     h->valid_ghost = 0;
     if (h->cfg.nranks > 1 && (h->cfg.flags & HEAT_FLAG_PEER_HALO) && !h->peer_ready) {
@@ -452,6 +579,16 @@ int heat_set_field(heat_handle* h, const void* src, int64_t src_pitch, int src_i
         h->valid_ghost = h->g;
     }
     CUDA_TRY(cudaMemcpyAsync(h->buf[1], h->buf[0], (size_t)h->lrows * row_bytes(h), cudaMemcpyDeviceToDevice, h->s_compute));
+    return HEAT_OK;
+}
+
+int heat_set_field(heat_handle* h, const void* src, int64_t src_pitch, int src_is_device) {
+    if (!h || !src) return fail(HEAT_ERR_INVALID, "heat_set_field: null argument");
+    if (src_pitch <= 0) src_pitch = h->ncols;
+    if (src_pitch < h->ncols) return fail(HEAT_ERR_INVALID, "heat_set_field: src_pitch %lld < own columns %d", (long long)src_pitch, h->ncols);
+    CUDA_TRY(cudaSetDevice(h->dev));
+    int rc = install_field(h, src, src_pitch, src_is_device);
+    if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(h->s_compute));
     return HEAT_OK;
 }
@@ -484,7 +621,7 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     if (!h) return fail(HEAT_ERR_NOMEM, "heat_init: out of host memory");
     h->cfg = *cfg;
     h->dev = cfg->device;
-    h->nx = cfg->nx;
+    h->gnx = cfg->nx;
     h->ny = cfg->ny;
     h->esize = cfg->dtype == HEAT_F32 ? 4 : 8;
     h->fma = (cfg->flags & HEAT_FLAG_FMAD) != 0;
@@ -492,16 +629,37 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     h->kflags = sweep_policy_flags();
     h->stream_rows = env_int("HEAT_STREAM_ROWS", 0);
     h->stream_threads = env_int("HEAT_STREAM_THREADS", 0);
-    int rc = heat_slab_partition(h->ny, cfg->nranks, cfg->rank, &h->row0, &h->nrows);
+    h->px = cfg->ranks_x > 0 ? cfg->ranks_x : 1;
+    if (cfg->nranks % h->px != 0) {
+        delete h;
+        return fail(HEAT_ERR_INVALID, "heat_init: ranks_x %d does not divide nranks %d", h->px, cfg->nranks);
+    }
+    h->py = cfg->nranks / h->px;
+    h->rxi = cfg->rank % h->px;
+    h->ryi = cfg->rank / h->px;
+    int rc = heat_tile_partition(h->gnx, h->ny, h->px, h->py, cfg->rank, &h->row0, &h->nrows, &h->col0, &h->ncols);
     if (rc) { delete h; return rc; }
     h->g = cfg->nranks > 1 ? (cfg->ghost > 0 ? cfg->ghost : 1) : 0;
-    // judged on the THINNEST slab of the partition, not on this rank's: every rank then takes the same
+    // judged on the THINNEST tile of the partition, not on this rank's: every rank then takes the same
     // decision and none is left waiting inside the collective calls below
-    if (cfg->nranks > 1 && h->ny / cfg->nranks < h->g) {
+    if ((h->py > 1 && h->ny / h->py < h->g) || (h->px > 1 && h->gnx / h->px < h->g)) {
         delete h;
-        return fail(HEAT_ERR_INVALID, "heat_init: the thinnest slab (%d rows of %d over %d ranks) is thinner than ghost depth %d",
-                    cfg->ny / cfg->nranks, cfg->ny, cfg->nranks, cfg->ghost > 0 ? cfg->ghost : 1);
+        return fail(HEAT_ERR_INVALID, "heat_init: the thinnest tile (%d rows x %d columns: %d x %d over %d x %d ranks) is thinner than ghost depth %d",
+                    cfg->ny / h->py, cfg->nx / h->px, cfg->ny, cfg->nx, h->py, h->px, h->g);
     }
+    if (h->px > 1 && (cfg->flags & HEAT_FLAG_PEER_HALO)) {
+        delete h;
+        return fail(HEAT_ERR_UNSUPPORTED, "heat_init: HEAT_FLAG_PEER_HALO serves row slabs only (ranks_x <= 1); the 2-D decomposition exchanges through NCCL");
+    }
+    if (h->px > 1 && cfg->ext_buf[0]) {
+        delete h;
+        return fail(HEAT_ERR_UNSUPPORTED, "heat_init: caller-owned buffers are not supported with ranks_x > 1");
+    }
+    h->gl = (h->px > 1 && h->rxi > 0) ? h->g : 0;
+    h->gr = (h->px > 1 && h->rxi + 1 < h->px) ? h->g : 0;
+    h->nx = h->ncols + h->gl + h->gr;
+    const bool has_rows_above_below = h->py > 1;
+    if (!has_rows_above_below && cfg->nranks > 1) { /* px x 1: ghost rows are allocated but never exchanged */ }
     if (h->g % h->tblock != 0 && cfg->nranks > 1) {
         delete h;
         return fail(HEAT_ERR_INVALID, "heat_init: ghost depth %d must be a multiple of tblock %d", h->g, h->tblock);
@@ -553,9 +711,18 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         INIT_TRY(cudaMemsetAsync(h->buf[1], 0, bytes, h->s_compute));
     }
 
+    if (h->px > 1)
+        for (void*& p : h->colbuf) INIT_TRY(cudaMalloc(&p, (size_t)h->lrows * h->g * h->esize));
     rc = resolve_kernel(h);
     if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
-    if (h->kernel == HEAT_KERNEL_TMA) {
+    if (h->kernel == HEAT_KERNEL_PERSIST) {
+        const size_t mb = persist_mailbox_bytes(h->nx, h->esize, h->sm_count);
+        INIT_TRY(cudaMalloc(&h->p_mailbox, mb));
+        INIT_TRY(cudaMalloc((void**)&h->p_flags, (size_t)h->sm_count * sizeof(unsigned)));
+        INIT_TRY(cudaMemsetAsync(h->p_flags, 0, (size_t)h->sm_count * sizeof(unsigned), h->s_compute));
+        h->persist_min_nt = env_int("HEAT_PERSIST_MIN_NT", 8);
+    }
+    if (h->kernel == HEAT_KERNEL_TMA || h->kernel == HEAT_KERNEL_PERSIST) {
         rc = tma_setup(h->tma, h->buf, cfg->dtype == HEAT_F32, h->nx, h->lrows, h->pitch, g_err);
         if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
     }
@@ -588,7 +755,7 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
         }
     }
     if (field) {
-        rc = heat_set_field(h, field, h->nx, 0);
+        rc = heat_set_field(h, field, h->ncols, 0);
         if (rc) { std::string keep = g_err; heat_destroy(h); g_err = keep; return rc; }
     }
     *out = h;
@@ -673,6 +840,9 @@ int heat_step(heat_handle* h, int nt) {
         if (h->kernel == HEAT_KERNEL_RESIDENT) {
             CUDA_TRY(HEAT_DISPATCH(h, launch_resident_t, h, h->buf[h->cur], h->buf[h->cur ^ 1], nt, h->s_compute));
             h->cur ^= 1;
+        } else if (h->kernel == HEAT_KERNEL_PERSIST && nt >= h->persist_min_nt) {
+            CUDA_TRY(HEAT_DISPATCH(h, launch_persist_t, h, h->buf[h->cur], h->buf[h->cur ^ 1], nt, h->s_compute));
+            h->cur ^= 1;
         } else if (!multi) {
             int t = 0;
             for (; h->tblock > 1 && t + h->tblock <= nt; t += h->tblock) {
@@ -686,7 +856,7 @@ int heat_step(heat_handle* h, int nt) {
                 if (serpentine_enabled()) h->kflags ^= KF_REVERSE;
             }
         } else {
-            const bool overlap = (h->cfg.flags & HEAT_FLAG_OVERLAP) && h->nrows >= 2 * h->g;
+            const bool overlap = (h->cfg.flags & HEAT_FLAG_OVERLAP) && h->nrows >= 2 * h->g && h->px == 1;
             const int own_lo = h->row0, own_hi = h->row0 + h->nrows - 1;
             for (int t = 0; t < nt;) {
                 int rc = wait_comm(h);
@@ -766,6 +936,60 @@ int heat_step(heat_handle* h, int nt) {
     return HEAT_OK;
 }
 
+// Job pipeline.  A job = upload this rank's rows, march nt steps, download the result.  Jobs submitted back to
+// back overlap: while job i marches on s_compute, job i+1's input crosses PCIe into `pipe_in` on s_h2d and job
+// i-1's result leaves from `pipe_out` on s_d2h (PCIe is full duplex).  The two staging buffers cost two device-
+// side copies per job (about 3 launch-times of the stencil kernel in total) and leave the stepping code untouched.
+int heat_submit(heat_handle* h, const void* host_src, int64_t src_pitch, int nt, void* host_dst) {
+    if (!h || !host_src || !host_dst) return fail(HEAT_ERR_INVALID, "heat_submit: null argument");
+    if (nt < 0) return fail(HEAT_ERR_INVALID, "heat_submit: nt must be >= 0 (got %d)", nt);
+    if (src_pitch <= 0) src_pitch = h->ncols;
+    if (src_pitch < h->ncols) return fail(HEAT_ERR_INVALID, "heat_submit: src_pitch %lld < own columns %d", (long long)src_pitch, h->ncols);
+    CUDA_TRY(cudaSetDevice(h->dev));
+    const size_t own_bytes = (size_t)h->nrows * row_bytes(h), dense = (size_t)h->ncols * h->esize;
+    const size_t goff = (size_t)h->gl * h->esize;            // own columns start here inside a local row
+    if (!h->pipe_in) {                       // first job: staging buffers, copy streams, events
+        CUDA_TRY(cudaMalloc(&h->pipe_in, own_bytes));
+        CUDA_TRY(cudaMalloc(&h->pipe_out, own_bytes));
+        CUDA_TRY(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+        for (cudaEvent_t* e : {&h->ev_up, &h->ev_in_free, &h->ev_res, &h->ev_out_free})
+            CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        CUDA_TRY(cudaMemsetAsync(h->pipe_in, 0, own_bytes, h->s_h2d));      // the pitch padding stays zero for good
+    }
+    // upload, once the previous job has taken its input out of pipe_in
+    if (h->pipe_jobs) CUDA_TRY(cudaStreamWaitEvent(h->s_h2d, h->ev_in_free, 0));
+    CUDA_TRY(copy_rows((char*)h->pipe_in + goff, row_bytes(h), host_src, (size_t)src_pitch * h->esize, dense, h->nrows,
+                       cudaMemcpyHostToDevice, h->s_h2d));
+    CUDA_TRY(cudaEventRecord(h->ev_up, h->s_h2d));
+    // install + march on the compute stream
+    CUDA_TRY(cudaStreamWaitEvent(h->s_compute, h->ev_up, 0));
+    int rc = install_field(h, (char*)h->pipe_in + goff, h->pitch, 1);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev_in_free, h->s_compute));
+    rc = heat_step(h, nt);
+    if (rc) return rc;
+    // result -> pipe_out once the previous job's download has drained it, then over PCIe on s_d2h
+    if (h->pipe_jobs) CUDA_TRY(cudaStreamWaitEvent(h->s_compute, h->ev_out_free, 0));
+    CUDA_TRY(cudaMemcpyAsync(h->pipe_out, row_ptr(h, h->cur, h->g), own_bytes, cudaMemcpyDeviceToDevice, h->s_compute));
+    CUDA_TRY(cudaEventRecord(h->ev_res, h->s_compute));
+    CUDA_TRY(cudaStreamWaitEvent(h->s_d2h, h->ev_res, 0));
+    CUDA_TRY(copy_rows(host_dst, dense, (char*)h->pipe_out + goff, row_bytes(h), dense, h->nrows, cudaMemcpyDeviceToHost, h->s_d2h));
+    CUDA_TRY(cudaEventRecord(h->ev_out_free, h->s_d2h));
+    h->pipe_jobs++;
+    return HEAT_OK;
+}
+
+int heat_drain(heat_handle* h) {
+    if (!h) return fail(HEAT_ERR_INVALID, "heat_drain: null handle");
+    CUDA_TRY(cudaSetDevice(h->dev));
+    if (h->s_h2d) CUDA_TRY(cudaStreamSynchronize(h->s_h2d));
+    CUDA_TRY(cudaStreamSynchronize(h->s_comm));
+    CUDA_TRY(cudaStreamSynchronize(h->s_compute));
+    if (h->s_d2h) CUDA_TRY(cudaStreamSynchronize(h->s_d2h));
+    return HEAT_OK;
+}
+
 int heat_sync(heat_handle* h) {
     if (!h) return fail(HEAT_ERR_INVALID, "heat_sync: null handle");
     CUDA_TRY(cudaSetDevice(h->dev));
@@ -780,10 +1004,11 @@ int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root) {
     int rc = wait_comm(h);
     if (rc) return rc;
     const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
-    const size_t dense = (size_t)h->nx * h->esize;
+    const size_t dense = (size_t)h->ncols * h->esize;        // this rank's own tile, dense
+    const size_t goff = (size_t)h->gl * h->esize;
     if (global_root < 0 || h->cfg.nranks == 1) {
         if (!dst) return fail(HEAT_ERR_INVALID, "heat_gather: null destination");
-        CUDA_TRY(copy_rows(dst, dense, row_ptr(h, h->cur, h->g), row_bytes(h), dense, h->nrows, kind, h->s_compute));
+        CUDA_TRY(copy_rows(dst, dense, row_ptr(h, h->cur, h->g) + goff, row_bytes(h), dense, h->nrows, kind, h->s_compute));
         CUDA_TRY(cudaStreamSynchronize(h->s_compute));
         return HEAT_OK;
     }
@@ -797,15 +1022,19 @@ int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root) {
         return HEAT_OK;
     }
     if (!dst) return fail(HEAT_ERR_INVALID, "heat_gather: root needs a destination");
+    const size_t gdense = (size_t)h->gnx * h->esize;         // a row of the global field
     for (int r = 0; r < h->cfg.nranks; ++r) {
-        int r0, nr;
-        heat_slab_partition(h->ny, h->cfg.nranks, r, &r0, &nr);
-        char* out = (char*)dst + (size_t)r0 * dense;
+        int r0, nr, c0, nc;
+        heat_tile_partition(h->gnx, h->ny, h->px, h->py, r, &r0, &nr, &c0, &nc);
+        char* out = (char*)dst + (size_t)r0 * gdense + (size_t)c0 * h->esize;
         if (r == h->cfg.rank) {
-            CUDA_TRY(copy_rows(out, dense, row_ptr(h, h->cur, h->g), row_bytes(h), dense, nr, kind, h->s_compute));
+            CUDA_TRY(copy_rows(out, gdense, row_ptr(h, h->cur, h->g) + goff, row_bytes(h), dense, nr, kind, h->s_compute));
             continue;
         }
-        const size_t need = (size_t)nr * row_bytes(h);
+        // the sender's local geometry (library-owned buffers: pitch = its local width rounded up to 16 elements)
+        const int rgl = (h->px > 1 && r % h->px > 0) ? h->g : 0, rgr = (h->px > 1 && r % h->px + 1 < h->px) ? h->g : 0;
+        const long rpitch = h->px > 1 ? ((long)(nc + rgl + rgr) + 15) / 16 * 16 : h->pitch;
+        const size_t need = (size_t)nr * rpitch * h->esize;
         if (need > h->stage_bytes) {
             CUDA_TRY(cudaStreamSynchronize(h->s_compute));
             cudaFree(h->d_stage);
@@ -814,8 +1043,9 @@ int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root) {
             CUDA_TRY(cudaMalloc(&h->d_stage, need));
             h->stage_bytes = need;
         }
-        NCCL_TRY(N.Recv(h->d_stage, (size_t)nr * h->pitch, dt, r, h->comm, h->s_compute));
-        CUDA_TRY(copy_rows(out, dense, h->d_stage, row_bytes(h), dense, nr, kind, h->s_compute));
+        NCCL_TRY(N.Recv(h->d_stage, (size_t)nr * rpitch, dt, r, h->comm, h->s_compute));
+        CUDA_TRY(copy_rows(out, gdense, (char*)h->d_stage + (size_t)rgl * h->esize, (size_t)rpitch * h->esize,
+                           (size_t)nc * h->esize, nr, kind, h->s_compute));
         CUDA_TRY(cudaStreamSynchronize(h->s_compute));
     }
     CUDA_TRY(cudaStreamSynchronize(h->s_compute));
@@ -831,9 +1061,9 @@ int heat_checksum(heat_handle* h, double* sum) {
     if (!h->d_sum) CUDA_TRY(cudaMalloc(&h->d_sum, sizeof(double)));
     const int yb = h->g, ye = h->g + h->nrows;
     if (h->cfg.dtype == HEAT_F32)
-        heat_sum_partial_kernel<float><<<kSumBlocks, 256, 0, h->s_compute>>>((const float*)h->buf[h->cur], h->nx, h->pitch, yb, ye, h->d_partials);
+        heat_sum_partial_kernel<float><<<kSumBlocks, 256, 0, h->s_compute>>>((const float*)h->buf[h->cur] + h->gl, h->ncols, h->pitch, yb, ye, h->d_partials);
     else
-        heat_sum_partial_kernel<double><<<kSumBlocks, 256, 0, h->s_compute>>>((const double*)h->buf[h->cur], h->nx, h->pitch, yb, ye, h->d_partials);
+        heat_sum_partial_kernel<double><<<kSumBlocks, 256, 0, h->s_compute>>>((const double*)h->buf[h->cur] + h->gl, h->ncols, h->pitch, yb, ye, h->d_partials);
     CUDA_TRY(cudaGetLastError());
     heat_sum_final_kernel<<<1, 32, 0, h->s_compute>>>(h->d_partials, kSumBlocks, h->d_sum);
     CUDA_TRY(cudaGetLastError());
@@ -844,7 +1074,9 @@ int heat_checksum(heat_handle* h, double* sum) {
 
 int heat_get_info(heat_handle* h, heat_info* info) {
     if (!h || !info) return fail(HEAT_ERR_INVALID, "heat_get_info: null argument");
-    info->nx = h->nx; info->ny = h->ny;
+    info->nx = h->gnx; info->ny = h->ny;
+    info->col0 = h->col0; info->ncols = h->ncols;
+    info->ghost_left = h->gl; info->local_nx = h->nx;
     info->row0 = h->row0; info->nrows = h->nrows;
     info->ghost = h->g;
     info->kernel = h->kernel; info->tblock = h->tblock;

@@ -219,10 +219,16 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     int seg = 0;
     if (const char* v = getenv("HEAT_TEMPORAL_SEG")) seg = atoi(v);
     if (seg <= 0) {
-        // Work items are warps; about 12 are resident per SM (3 CTAs, shared-memory bound).  Prefer a whole
-        // number of waves (3, 2 or 1) with segments long enough that the 2K re-read rows stay cheap; a grid
-        // too small for that gets exactly one wave, whatever the segment length.
+        // Work items are warps; about 12 are resident per SM (3 CTAs, shared-memory bound).  As in the CTA-level
+        // kernel, short segments issued strip-fastest sweep the field as a thin wavefront, which DRAM likes (16384^2
+        // fp64 k=2: 1024-row segments 641 GLUPS, 44 -> 790, 14 -> 856, 11 -> 869, 8 -> 796; profiles/README.md, round 2) — but every
+        // segment recomputes 2K rows of pipeline fill, so the best length grows with K: k=4 fp64 peaks at ~160 rows
+        // (1492 GLUPS), fp32 at ~88.  That needs a grid of several waves; smaller grids keep whole waves instead.
         const int resident = sm_count * 12;
+        const int pref = K == 1 ? 14 : K == 2 ? (sizeof(T) == 8 ? 11 : 14) : (sizeof(T) == 8 ? 160 : 88);
+        if ((long)nstrips * ((rows + pref - 1) / pref) >= 3L * resident) seg = pref;
+        // Otherwise prefer a whole number of waves (3, 2 or 1) with segments long enough that the 2K re-read rows
+        // stay cheap; a grid too small for that gets exactly one wave, whatever the segment length.
         for (int w = 3; w >= 1 && seg <= 0; --w) {
             const int nseg = std::max(1, w * resident / nstrips);
             const int cand = (rows + nseg - 1) / nseg;

@@ -401,14 +401,15 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     if (e != cudaSuccess) return e;
     const int rows = ye - yb;
     const int gx = (int)((pitch + kTmaBX - 1) / kTmaBX);
+    // Segment length.  SHORT segments, issued strip-fastest, make the resident CTAs a thin wavefront that sweeps the
+    // field row band by row band: DRAM sees two compact streams (one read, one write) instead of ~13 scattered ones,
+    // the two halo rows a segment shares with its neighbours are L2 hits, and the tail of the grid is short.  Measured
+    // on B200 at 16384^2 fp64 (profiles/README.md, round 2): 1264-row segments 387 GLUPS, 94 -> 423, 46 -> 433,
+    // 30 -> 431, 16 -> 292 (per-CTA prologue dominates).  46 = 3 stages of 16 input rows exactly (46 + 2 halo rows).
     int seg = 0;
     if (const char* v = getenv("HEAT_TMA_SEG")) seg = atoi(v);
-    if (seg <= 0) {
-        const int target = sm_count * 12;
-        const int nseg = std::max(1, target / gx);
-        seg = (rows + nseg - 1) / nseg;
-        seg = std::max(64, (seg + kTmaBY - 1) / kTmaBY * kTmaBY);
-    }
+    if (seg <= 0) seg = 3 * kTmaBY - 2;
+    (void)sm_count;
     seg = std::min(seg, rows);
     const int gy = (rows + seg - 1) / seg;
     return launch_pdl(k, dim3(gx, gy), dim3(kTmaThreads), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg, rx, ry, kflags, dst2, shift2);

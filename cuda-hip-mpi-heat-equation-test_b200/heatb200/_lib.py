@@ -14,12 +14,12 @@ LIB_PATH = os.path.join(HERE, "libheat.so")
 HEAT_OK, ERR_INVALID, ERR_CUDA, ERR_NCCL, ERR_NOMEM, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 F64, F32 = 0, 1
 ORDER_FORTRAN, ORDER_PYCUDA, ORDER_PYSERIAL = 0, 1, 2
-KERNEL_AUTO, KERNEL_SIMPLE, KERNEL_STREAM, KERNEL_TMA, KERNEL_RESIDENT, KERNEL_WTMA = 0, 1, 2, 3, 4, 5
+KERNEL_AUTO, KERNEL_SIMPLE, KERNEL_STREAM, KERNEL_TMA, KERNEL_RESIDENT, KERNEL_WTMA, KERNEL_PERSIST = 0, 1, 2, 3, 4, 5, 6
 FLAG_FMAD, FLAG_OVERLAP, FLAG_SKIP_EXCHANGE, FLAG_PEER_HALO = 1, 2, 4, 8
 
 ORDERS = {"fortran": ORDER_FORTRAN, "pycuda": ORDER_PYCUDA, "pyserial": ORDER_PYSERIAL}
 KERNELS = {"auto": KERNEL_AUTO, "simple": KERNEL_SIMPLE, "stream": KERNEL_STREAM, "tma": KERNEL_TMA,
-           "resident": KERNEL_RESIDENT, "wtma": KERNEL_WTMA}
+           "resident": KERNEL_RESIDENT, "wtma": KERNEL_WTMA, "persist": KERNEL_PERSIST}
 KERNEL_NAMES = {v: k for k, v in KERNELS.items()}
 
 
@@ -36,6 +36,7 @@ class HeatConfig(C.Structure):
         ("rx", C.c_double), ("ry", C.c_double), ("device", C.c_int32), ("rank", C.c_int32),
         ("nranks", C.c_int32), ("ghost", C.c_int32), ("nccl_id", C.c_void_p),
         ("ext_buf", C.c_void_p * 2), ("ext_pitch", C.c_int64), ("stream", C.c_uint64),
+        ("ranks_x", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 
@@ -44,6 +45,7 @@ class HeatInfo(C.Structure):
         ("nx", C.c_int32), ("ny", C.c_int32), ("row0", C.c_int32), ("nrows", C.c_int32),
         ("ghost", C.c_int32), ("kernel", C.c_int32), ("tblock", C.c_int32), ("pitch", C.c_int64),
         ("buf", C.c_void_p * 2), ("current", C.c_int32), ("device", C.c_int32),
+        ("col0", C.c_int32), ("ncols", C.c_int32), ("ghost_left", C.c_int32), ("local_nx", C.c_int32),
     ]
 
 
@@ -64,6 +66,8 @@ PROTOTYPES = {
     "heat_peer_export": (C.c_int, [_H, C.c_void_p]),
     "heat_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
     "heat_gather": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_int]),
+    "heat_submit": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
+    "heat_drain": (C.c_int, [_H]),
     "heat_checksum": (C.c_int, [_H, C.POINTER(C.c_double)]),
     "heat_checksum_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
                                         C.c_void_p, C.c_uint64]),
@@ -74,6 +78,7 @@ PROTOTYPES = {
     "heat_last_error": (C.c_char_p, []),
     "heat_version": (C.c_char_p, []),
     "heat_slab_partition": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "heat_tile_partition": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 4),
     "heat_derive_fortran": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double,
                                       C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "heat_nccl_unique_id": (C.c_int, [C.c_void_p]),

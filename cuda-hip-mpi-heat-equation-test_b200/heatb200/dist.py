@@ -47,6 +47,31 @@ def my_rows(ny: int):
     return _solver.slab_partition(ny, dist.get_world_size(), dist.get_rank())
 
 
+def my_tile(nx: int, ny: int, ranks_x: int):
+    """This rank's (row0, nrows, col0, ncols) in a ranks_x x (world / ranks_x) decomposition."""
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    return _solver.tile_partition(nx, ny, ranks_x, world // ranks_x, dist.get_rank())
+
+
+def tile_solver(field_tile: np.ndarray, nx_global: int, ny_global: int, ranks_x: int, rx, ry=None, *,
+                nccl_id: bytes | None = None, device: int | None = None, **kw) -> "_solver.HeatSolver":
+    """HeatSolver for this rank's tile of a [ny_global, nx_global] field cut into ranks_x x (world / ranks_x) tiles
+    (rank = ry * ranks_x + rx); collective.  Halos travel through NCCL: rows directly, columns packed.
+    ref: the second decomposition direction the reference reserves, fortran/mpi+cuda/heat.F90:28-29,87-97."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if nccl_id is None and world > 1:
+        nccl_id = shared_nccl_id()
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    kw.pop("peer_halo", None)
+    s = _solver.HeatSolver(field_tile, rx, ry, nx=nx_global, ny=ny_global, rank=rank, nranks=world, nccl_id=nccl_id,
+                           device=device, ranks_x=ranks_x, **kw)
+    s.halo_mode = "NCCL send/recv, %d x %d tiles" % (ranks_x, world // ranks_x)
+    return s
+
+
 def slab_solver(field_slab: np.ndarray, ny_global: int, rx, ry=None, *, nccl_id: bytes | None = None,
                 device: int | None = None, **kw) -> "_solver.HeatSolver":
     """HeatSolver for this rank's slab of a [ny_global, nx] field; collective."""

@@ -20,6 +20,13 @@ def slab_partition(ny: int, nranks: int, rank: int):
     return r0.value, nr.value
 
 
+def tile_partition(nx: int, ny: int, ranks_x: int, ranks_y: int, rank: int):
+    """(row0, nrows, col0, ncols) of `rank` = ry * ranks_x + rx in a ranks_x x ranks_y decomposition."""
+    v = [C.c_int() for _ in range(4)]
+    check(lib().heat_tile_partition(nx, ny, ranks_x, ranks_y, rank, *[C.byref(x) for x in v]))
+    return tuple(x.value for x in v)
+
+
 def nccl_unique_id() -> bytes:
     _lib.preload_nccl()
     buf = C.create_string_buffer(128)
@@ -41,12 +48,15 @@ class HeatSolver:
 
     def __init__(self, field, rx, ry=None, *, nx=None, ny=None, dtype=None, order="fortran", kernel="auto",
                  tblock=1, fmad=False, device=0, rank=0, nranks=1, ghost=0, overlap=False,
-                 skip_exchange=False, peer_halo=False, nccl_id: bytes | None = None, buffers=None, stream=0):
+                 skip_exchange=False, peer_halo=False, nccl_id: bytes | None = None, buffers=None, stream=0,
+                 ranks_x=1):
         self._h = C.c_void_p()
+        ranks_x = max(1, int(ranks_x))
         if field is not None:
             field = np.ascontiguousarray(field)
             dtype = field.dtype
-            nx = field.shape[1]
+            if ranks_x == 1:
+                nx = field.shape[1]
             if nranks == 1:
                 ny = field.shape[0]
         if nx is None or ny is None or dtype is None:
@@ -55,7 +65,7 @@ class HeatSolver:
         if dtype not in _DTYPES:
             raise TypeError("HeatSolver: dtype must be float64 or float32, got %s" % dtype)
         self.dtype, self.nx, self.ny = dtype, int(nx), int(ny)
-        self.rank, self.nranks = rank, nranks
+        self.rank, self.nranks, self.ranks_x = rank, nranks, ranks_x
         cfg = HeatConfig()
         cfg.struct_size = C.sizeof(HeatConfig)
         cfg.nx, cfg.ny, cfg.dtype = self.nx, self.ny, _DTYPES[dtype]
@@ -80,11 +90,14 @@ class HeatSolver:
             cfg.ext_buf[0], cfg.ext_buf[1] = b0.data_ptr(), b1.data_ptr()
             cfg.ext_pitch = b0.shape[1]
         cfg.stream = int(stream)
-        if field is not None:
-            r0, nr = slab_partition(self.ny, nranks, rank)
-            if field.shape != (nr, self.nx):
-                raise ValueError("HeatSolver: rank %d owns rows [%d, %d): expected field shape %s, got %s"
-                                 % (rank, r0, r0 + nr, (nr, self.nx), field.shape))
+        cfg.ranks_x = ranks_x
+        if nranks % ranks_x:
+            raise ValueError("HeatSolver: ranks_x %d does not divide nranks %d" % (ranks_x, nranks))
+        r0, nr, c0, nc = tile_partition(self.nx, self.ny, ranks_x, nranks // ranks_x, rank)
+        self.tile = (r0, nr, c0, nc)
+        if field is not None and field.shape != (nr, nc):
+            raise ValueError("HeatSolver: rank %d owns rows [%d, %d) x columns [%d, %d): expected field shape %s, got %s"
+                             % (rank, r0, r0 + nr, c0, c0 + nc, (nr, nc), field.shape))
         ptr = field.ctypes.data_as(C.c_void_p) if field is not None else None
         check(lib().heat_init(C.byref(self._h), C.byref(cfg), ptr))
 
@@ -101,7 +114,7 @@ class HeatSolver:
         info = self.info()
         if root is None:
             if out is None:
-                out = np.empty((info.nrows, self.nx), dtype=self.dtype)
+                out = np.empty((info.nrows, info.ncols), dtype=self.dtype)
             check(lib().heat_gather(self._h, out.ctypes.data_as(C.c_void_p), 0, -1))
             return out
         if self.rank == root:
@@ -115,6 +128,21 @@ class HeatSolver:
     def set_field(self, field: np.ndarray) -> None:
         field = np.ascontiguousarray(field, dtype=self.dtype)
         check(lib().heat_set_field(self._h, field.ctypes.data_as(C.c_void_p), field.shape[1], 0))
+
+    def submit(self, field: np.ndarray, nt: int, out: np.ndarray) -> None:
+        """Queue one job — upload `field` (this rank's rows), advance nt steps, download into `out` — without
+        waiting.  Back-to-back jobs overlap their PCIe copies with each other's march (heat_submit); give pinned
+        arrays.  `field` and `out` belong to the library until drain() returns."""
+        if field.dtype != self.dtype or out.dtype != self.dtype or not field.flags.c_contiguous or not out.flags.c_contiguous:
+            raise ValueError("HeatSolver.submit: field and out must be C-contiguous arrays of dtype %s" % self.dtype)
+        if field.shape != out.shape or field.shape != (self.tile[1], self.tile[3]):
+            raise ValueError("HeatSolver.submit: field and out must both be this rank's tile %s" % ((self.tile[1], self.tile[3]),))
+        check(lib().heat_submit(self._h, field.ctypes.data_as(C.c_void_p), field.shape[1], int(nt),
+                                out.ctypes.data_as(C.c_void_p)))
+
+    def drain(self) -> None:
+        """Wait for every submitted job (uploads, marches, downloads)."""
+        check(lib().heat_drain(self._h))
 
     def peer_export(self) -> bytes:
         """This rank's CUDA-IPC blob (buffers + flag words) for its neighbours (peer_halo=True only)."""

@@ -53,6 +53,9 @@ extern "C" {
 #define HEAT_KERNEL_RESIDENT 4  /* whole field in one CTA's shared memory, all steps in 1 launch */
 #define HEAT_KERNEL_WTMA    5   /* one private TMA pipeline per WARP, rows rotate through registers
                                    (the temporal-blocking kernel, also used for single steps)     */
+#define HEAT_KERNEL_PERSIST 6   /* field resident in the shared memory of ALL SMs (one row slab per CTA), all
+                                   steps of a heat_step call in ONE cooperative launch, neighbour CTAs trade
+                                   ghost rows through L2 (calls shorter than 8 steps use the TMA kernel)     */
 
 /* flags */
 #define HEAT_FLAG_FMAD          1u  /* FMA contraction.  Default (flag clear) is every add/mul individually rounded:
@@ -92,6 +95,11 @@ typedef struct heat_config {
                               [(rows + 2g)][ext_pitch]; caller keeps them alive until heat_destroy   */
     int64_t  ext_pitch;    /* row pitch of ext_buf in ELEMENTS (>= nx)                               */
     uint64_t stream;       /* optional cudaStream_t to run on (0: the library creates its own)       */
+    int32_t  ranks_x;      /* 2-D decomposition: ranks along x (0 or 1 = row slabs, the default and the fast
+                              path); nranks must be a multiple; rank = ry * ranks_x + rx owns the tile
+                              heat_tile_partition() gives it.  ref: ndims / nblocks / MPI_Dims_create,
+                              fortran/mpi+cuda/heat.F90:28-29,87-97                                  */
+    int32_t  reserved0;
 } heat_config;
 
 typedef struct heat_info {
@@ -103,6 +111,9 @@ typedef struct heat_info {
     void*   buf[2];            /* device pointers of the two ping-pong buffers                       */
     int32_t current;           /* which of buf[] holds the current field                             */
     int32_t device;
+    int32_t col0, ncols;       /* this rank's columns [col0, col0+ncols) (the whole width for row slabs)             */
+    int32_t ghost_left;        /* ghost columns held left of the own ones; local rows are local_nx wide              */
+    int32_t local_nx;
 } heat_info;
 
 typedef struct heat_timing {
@@ -152,6 +163,19 @@ int heat_peer_attach(heat_handle* h, const void* up_blob, const void* down_blob)
  * ref: D2H of python/cuda/cuda.py:99,102; T = Td fortran/mpi+cuda/heat.F90:261. */
 int heat_gather(heat_handle* h, void* dst, int dst_is_device, int global_root);
 
+/* Job pipeline: heat_submit = heat_set_field(host_src) + heat_step(nt) + heat_gather(host_dst) for this rank's
+ * rows, fully asynchronous.  Jobs submitted back to back overlap on the GPU: the next job's rows cross PCIe
+ * (host -> device) and the previous job's result leaves (device -> host) on two copy streams while the current
+ * job marches, through two device staging buffers the first call allocates (2 x this rank's rows).  Use PINNED
+ * host memory (pageable memory makes the copies synchronous and nothing overlaps).  host_src must stay unchanged
+ * and host_dst must not be read until heat_drain — which waits for every submitted job — has returned; the
+ * same host_dst may be given to several jobs (their downloads are ordered).  With nranks>1 every rank submits the
+ * same sequence of jobs (each includes the collective ghost fill).
+ * ref: the per-launch host<->device traffic of python/cuda/cuda.py:99 (drv.InOut / drv.In) — here once per
+ * job instead of three times per time step, and hidden behind the previous job's march. */
+int heat_submit(heat_handle* h, const void* host_src, int64_t src_pitch, int nt, void* host_dst);
+int heat_drain(heat_handle* h);
+
 /* Sum of this rank's own cells, deterministic (fixed reduction tree), as fp64.
  * ref: the commented-out debug check fortran/mpi+cuda/heat.F90:266-273. */
 int heat_checksum(heat_handle* h, double* sum);
@@ -189,6 +213,13 @@ const char* heat_version(void);
 /* Rows [row0, row0+nrows) of a ny-row field owned by `rank` of `nranks`; the remainder ny % nranks is
  * spread over the first ranks.  ref: nx = n/nblocks(1), fortran/mpi+cuda/heat.F90:92 (which drops it). */
 int heat_slab_partition(int ny, int nranks, int rank, int* row0, int* nrows);
+
+/* The tile of `rank` = ry * ranks_x + rx in a ranks_x x ranks_y decomposition: rows as heat_slab_partition(ny,
+ * ranks_y, ry), columns as heat_slab_partition(nx, ranks_x, rx).  With ranks_x > 1 every `field` / `src` / `dst`
+ * of heat_init, heat_set_field, heat_submit and heat_gather (global_root < 0) is this tile, dense [nrows][ncols].
+ * ref: MPI_Dims_create / mpi_cart_create, fortran/mpi+cuda/heat.F90:87-97 (the reference reserves the second
+ * dimension in ndims / nblocks, :28-29, and splits only one). */
+int heat_tile_partition(int nx, int ny, int ranks_x, int ranks_y, int rank, int* row0, int* nrows, int* col0, int* ncols);
 
 /* delta, dt, r with the reference's exact operation sequence.  ref: fortran/serial/heat.f90:15,17,59. */
 int heat_derive_fortran(int n, double sigma, double nu, double dom_len, double* delta, double* dt, double* r);

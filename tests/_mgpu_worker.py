@@ -15,7 +15,7 @@ import torch.distributed as dist  # noqa: E402
 
 import heatb200  # noqa: E402
 from heatb200 import dist as hd  # noqa: E402
-from oracle import heat_oracle as ho  # noqa: E402
+from oracle import c_oracle, heat_oracle as ho  # noqa: E402
 
 R100 = 0.24999999999999997
 
@@ -39,7 +39,16 @@ def main():
         (203, 130, 23, 4, True, 2, "tma", np.float64, True),
         (1024, 2048, 33, 16, True, 1, "tma", np.float64, True),
         (512, 1000, 37, 8, True, 4, "wtma", np.float32, True),
+        # the bench's settings: ghost 32, and rows as wide as the strong-scaling workload's (32768 columns =
+        # 256 strips, another grid shape for the TMA kernels' segment choice), k = 1, 2, 4, both halo modes
+        (1024, 32768, 70, 32, True, 1, "tma", np.float64, True),
+        (1024, 32768, 70, 32, True, 4, "tma", np.float64, True),
+        (1024, 32768, 69, 32, True, 1, "tma", np.float64),
+        (2048, 16384, 75, 32, True, 2, "tma", np.float32, True),
+        (8191, 4096, 69, 32, True, 1, "tma", np.float64, True),      # the case bench.py re-checks after its timed region
+        (8191, 4096, 70, 32, False, 4, "tma", np.float64, True),
     ]
+    c_oracle.threads(max(1, (os.cpu_count() or 1) // max(world, 1)), omp=True)   # torchrun exports OMP_NUM_THREADS=1
     for ci, case in enumerate(cases):
         ny, nx, steps, g, overlap, k, kernel, dtype = case[:8]
         peer = len(case) > 8 and case[8]
@@ -60,7 +69,10 @@ def main():
         cks = torch.tensor([ck], dtype=torch.float64, device="cuda")
         dist.all_reduce(cks)
         if rank == 0:
-            want = ho.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437))
+            if ny * nx > (1 << 22):      # big cases: the C restatement (bit-equal to the NumPy one, tests/test_oracle.py)
+                want = c_oracle.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437), omp=True)
+            else:
+                want = ho.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437))
             one = heatb200.march(full, steps, R100, 0.2437, order="pyserial", kernel=kernel, tblock=k, device=local)
             checks = {
                 "global_vs_oracle": np.array_equal(got.view(np.uint8), want.view(np.uint8)),
@@ -75,6 +87,64 @@ def main():
                                  "one!=want at %s" % np.argwhere(one != want)[:6].tolist(),
                                  "local!=want at %s" % np.argwhere(local_rows != want[r0:r0 + nr])[:6].tolist()))
             print("case %d%s %s exchanges=%d launches=%d" % (ci, " (peer)" if peer else "", "ok" if ok else "FAIL", t.halo_exchanges, t.kernel_launches), flush=True)
+    # job pipeline over the ranks (heat_submit / heat_drain): two different fields queued back to back; every rank
+    # checks its own rows of both results against the oracle
+    for peer in (False, True):
+        ny, nx, steps = 512, 1000, 21
+        fields = [1.0 + np.random.default_rng(300 + j).random((ny, nx)) for j in range(2)]
+        r0, nr = hd.my_rows(ny)
+        s = hd.slab_solver(fields[0][r0:r0 + nr], ny, R100, 0.2437, nccl_id=hd.shared_nccl_id(), device=local,
+                           order="pyserial", kernel="tma", tblock=2, ghost=8, overlap=True, peer_halo=peer)
+        outs = [np.empty((nr, nx)) for _ in range(2)]
+        for j in range(2):
+            s.submit(np.ascontiguousarray(fields[j][r0:r0 + nr]), steps, outs[j])
+        s.drain()
+        s.close()
+        bad = sum(not np.array_equal(outs[j], ho.march(fields[j], steps, ho.ORDER_PYSERIAL, R100, 0.2437)[r0:r0 + nr])
+                  for j in range(2))
+        t = torch.tensor([bad], device="cuda")
+        dist.all_reduce(t)
+        if rank == 0:
+            print("pipeline%s %s" % (" (peer)" if peer else "", "ok" if int(t.item()) == 0 else "FAIL"), " ", flush=True)
+            if int(t.item()):
+                failures.append(("pipeline", peer, int(t.item())))
+    # 2-D (px x py) decomposition: tiles with ghost rows AND ghost columns (columns travel packed), every px > 1
+    # that divides the world size — 2 x 1 on two GPUs, 2 x 2 and 4 x 1 on four, 2 x 4, 4 x 2 and 8 x 1 on eight
+    tile_cases = [
+        # (ny, nx, steps, ghost, tblock, kernel, dtype)
+        (64, 96, 9, 1, 1, "simple", np.float64),
+        (203, 260, 23, 4, 1, "tma", np.float64),
+        (512, 1000, 37, 8, 2, "tma", np.float32),
+        (1024, 2048, 35, 16, 4, "tma", np.float64),
+        (777, 4096, 70, 32, 1, "stream", np.float64),
+    ]
+    for px in [d for d in range(2, world + 1) if world % d == 0]:
+        for ci, (ny, nx, steps, g, k, kernel, dtype) in enumerate(tile_cases):
+            if nx // px < g or ny // (world // px) < g:
+                continue
+            full = (1.0 + np.random.default_rng(500 + ci).random((ny, nx))).astype(dtype)
+            r0, nr, c0, nc = hd.my_tile(nx, ny, px)
+            s = hd.tile_solver(full[r0:r0 + nr, c0:c0 + nc], nx, ny, px, R100, 0.2437, nccl_id=hd.shared_nccl_id(), device=local,
+                               order="pyserial", kernel=kernel, tblock=k, ghost=g)
+            s.step(steps // 2)
+            if ci % 2:
+                s.halo_exchange()
+            s.step(steps - steps // 2)
+            got = s.gather(root=0)
+            mine = s.gather()
+            ck = s.checksum()
+            s.close()
+            want = c_oracle.march(full, steps, ho.ORDER_PYSERIAL, dtype(R100), dtype(0.2437), omp=True)
+            bad = int(not np.array_equal(mine, want[r0:r0 + nr, c0:c0 + nc]))
+            bad += int(abs(ck - float(want[r0:r0 + nr, c0:c0 + nc].astype(np.float64).sum())) > 1e-9 * abs(ck))
+            if rank == 0:
+                bad += int(not np.array_equal(got.view(np.uint8), want.view(np.uint8)))
+            t = torch.tensor([bad], device="cuda")
+            dist.all_reduce(t)
+            if rank == 0:
+                print("tiles %dx%d case %d %s" % (px, world // px, ci, "ok" if int(t.item()) == 0 else "FAIL"), " ", flush=True)
+                if int(t.item()):
+                    failures.append(("tiles", px, ci, int(t.item())))
     flag = torch.tensor([len(failures)], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()

@@ -167,6 +167,46 @@ def test_boundary_ring_is_preserved_exactly():
             assert_bit_equal(got[sl], u0[sl])
 
 
+# ------------------------------------------------------------------ on-chip persistent stepping (one launch for all steps)
+@pytest.mark.parametrize("order", ORDERS)
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_persist_kernel_bit_exact(order, dtype):
+    """PERSIST: the field lives in the shared memory of all SMs (a row slab per CTA), neighbour CTAs trade ghost
+    rows through L2 every G steps.  Same bits as the oracle for ragged slabs, step counts that are and are not
+    multiples of the ghost depth, very few rows per CTA, and odd widths."""
+    for shape, nt in [((130, 257), 8), ((515, 300), 37), ((300, 1000), 9), ((1024, 1024), 30), ((149, 64), 21), ((2000, 130), 16)]:
+        u0 = rand_field(shape, dtype, seed=shape[0] + nt)
+        rx, ry = dtype(R100), dtype(0.2437)
+        want = c_oracle.march(u0, nt, ho.ORDERS[order], rx, ry)
+        with heatb200.HeatSolver(u0, float(rx), float(ry), order=order, kernel="persist") as s:
+            assert s.kernel_name == "persist"
+            s.step(nt)
+            assert s.timing().kernel_launches == 1                     # all nt steps in ONE launch
+            assert_bit_equal(s.gather(), want)
+
+
+def test_persist_kernel_repeated_calls_short_calls_and_auto():
+    u0 = rand_field((1024, 1024), seed=5)
+    u0[0, :] = 3.5
+    u0[:, -1] = -2.0                                                   # a ring that is not 1: must survive
+    with heatb200.HeatSolver(u0, R100) as s:                           # AUTO: too big for one CTA, fits the SMs
+        assert s.kernel_name == "persist"
+        for _ in range(6):
+            s.step(25)                                                 # flag epochs continue across launches
+        s.step(3)                                                      # short call: per-step launches (TMA kernel)
+        s.step(0)
+        assert s.timing().kernel_launches == 6 + 3
+        got = s.gather()
+    assert_bit_equal(got, c_oracle.march(u0, 153, 0, R100, omp=True))
+    for sl in [(0, slice(None)), (-1, slice(None)), (slice(None), 0), (slice(None), -1)]:
+        assert_bit_equal(got[sl], u0[sl])
+    got = heatb200.march(u0, 40, R100, order="pycuda", kernel="persist", fmad=True)
+    assert_bit_equal(got, c_oracle.march(u0, 40, ho.ORDER_PYCUDA, R100, contract=True))
+    with pytest.raises(heatb200.HeatError) as e:                       # 4096^2 does not fit on chip
+        heatb200.HeatSolver(None, 0.25, nx=4096, ny=4096, dtype=np.float64, kernel="persist")
+    assert e.value.code == _lib.ERR_UNSUPPORTED
+
+
 # ------------------------------------------------------------------ temporal blocking (k fused steps)
 @pytest.mark.parametrize("k", [2, 4])
 @pytest.mark.parametrize("order", ORDERS)
@@ -333,6 +373,51 @@ def test_16384_random_field_kernels_agree_and_linear():
     assert_bit_equal(res["tma"][1006:1006 + 64].cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("dtype,k", [(np.float64, 2), (np.float64, 4), (np.float32, 1), (np.float32, 2), (np.float32, 4)])
+def test_16384_bands_vs_c_oracle_temporal_and_fp32(dtype, k):
+    """What bench.py reports at 16384^2 beyond fp64 k=1: k = 2, 4 and fp32.  Three 256-row bands over the full
+    width — the top one including the Dirichlet row, one in the middle, the bottom one including the last row —
+    against the C oracle (a band cut `steps` rows deeper than what is compared is independent of the rest), and
+    the whole field against the single-step STREAM kernel."""
+    import torch
+    n, steps, B = 16384, 8, 256
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    g = torch.Generator(device="cuda").manual_seed(7)
+    u = 1.0 + torch.rand((n, n), dtype=tdt, device="cuda", generator=g)
+    u[0, :] = 1.0
+    u[-1, :] = 1.0
+    u[:, 0] = 1.0
+    u[:, -1] = 1.0
+    outs = {}
+    for kernel, kk in (("tma", k), ("stream", 1)):
+        with heatb200.HeatSolver(None, R100, nx=n, ny=n, dtype=dtype, kernel=kernel, tblock=kk) as s:
+            s.set_field_from_tensor(u)
+            s.step(steps)
+            out = torch.empty_like(u)
+            s.gather_into_tensor(out)
+            outs[kernel] = out
+    assert torch.equal(outs["tma"], outs["stream"])
+    got = outs["tma"]
+    r = dtype(R100)
+    top = c_oracle.march(u[:B + steps].cpu().numpy(), steps, 0, r, omp=True)[:B]
+    assert_bit_equal(got[:B].cpu().numpy(), top)
+    m0 = 7000
+    mid = c_oracle.march(u[m0 - steps:m0 + B + steps].cpu().numpy(), steps, 0, r, omp=True)[steps:-steps]
+    assert_bit_equal(got[m0:m0 + B].cpu().numpy(), mid)
+    bot = c_oracle.march(u[n - B - steps:].cpu().numpy(), steps, 0, r, omp=True)[steps:]
+    assert_bit_equal(got[n - B:].cpu().numpy(), bot)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_32768_wide_rows_every_kernel(dtype):
+    """Rows as wide as the strong-scaling workload's (32768 columns = 256 strips of the TMA kernels: a grid shape
+    of its own for their segment choice), 600 rows, against the C oracle."""
+    u0 = rand_field((600, 32768), dtype, seed=33)
+    want = c_oracle.march(u0, 9, 0, dtype(R100), omp=True)
+    for kernel, k in (("tma", 1), ("tma", 2), ("tma", 4), ("wtma", 1), ("stream", 1)):
+        assert_bit_equal(heatb200.march(u0, 9, float(dtype(R100)), kernel=kernel, tblock=k), want)
+
+
 # ------------------------------------------------------------------ torch buffers, checksum, errors
 def test_external_torch_buffers_and_unaligned_pitch():
     import torch
@@ -357,6 +442,35 @@ def test_external_torch_buffers_and_unaligned_pitch():
             with heatb200.HeatSolver(v0, R100, 0.2437, order="pyserial", buffers=(c0, c1), kernel=kern, tblock=2) as s2:
                 s2.step(7)
                 assert_bit_equal(s2.gather(), ho.march(v0, 7, ho.ORDER_PYSERIAL, R100, 0.2437))
+
+
+@pytest.mark.parametrize("shape,dtype,k", [((300, 520), np.float64, 1), ((131, 1001), np.float64, 2), ((260, 512), np.float32, 4)])
+def test_job_pipeline_matches_blocking_calls(shape, dtype, k):
+    """heat_submit / heat_drain: back-to-back jobs (upload, march, download overlapped across jobs) give the bits
+    of the blocking set_field + step + gather sequence and of the oracle; pinned and pageable host memory."""
+    import torch
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    njobs = 4
+    ins = [torch.empty(shape, dtype=tdt).pin_memory().numpy() for _ in range(njobs)]
+    outs = [torch.empty(shape, dtype=tdt).pin_memory().numpy() for _ in range(njobs)]
+    for i, a in enumerate(ins):
+        a[...] = rand_field(shape, dtype, seed=40 + i)
+    ins[3] = np.array(ins[3])                                   # one pageable input
+    with heatb200.HeatSolver(ins[0], float(dtype(R100)), kernel="tma", tblock=k) as s:
+        for i in range(njobs):
+            s.submit(ins[i], 5 + i, outs[i])
+        s.drain()
+        for i in range(njobs):
+            assert_bit_equal(outs[i], ho.march(ins[i], 5 + i, 0, dtype(R100)))
+        # the handle is still an ordinary solver afterwards, and one output buffer may serve several jobs
+        s.step(2)
+        assert_bit_equal(s.gather(), ho.march(ins[3], 5 + 3 + 2, 0, dtype(R100)))
+        s.submit(ins[0], 3, outs[0])
+        s.submit(ins[1], 3, outs[0])
+        s.drain()
+        assert_bit_equal(outs[0], ho.march(ins[1], 3, 0, dtype(R100)))
+        with pytest.raises(ValueError):
+            s.submit(ins[0][:-1], 1, outs[0])
 
 
 def test_checksum_deterministic_and_close():

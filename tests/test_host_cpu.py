@@ -37,7 +37,31 @@ def test_config_struct_matches_header_layout():
     h = C.c_void_p()
     rc = heatb200.lib().heat_init(C.byref(h), C.byref(cfg), None)
     assert rc == _lib.ERR_INVALID and b"struct_size" in heatb200.lib().heat_last_error()
-    assert C.sizeof(_lib.HeatConfig) == 104
+    assert C.sizeof(_lib.HeatConfig) == 112
+
+
+def test_tile_partition_and_argument_checks():
+    from heatb200.solver import tile_partition
+    nx, ny = 1000, 203
+    for px, py in [(1, 4), (2, 2), (4, 2), (8, 1), (3, 5)]:
+        tiles = [tile_partition(nx, ny, px, py, r) for r in range(px * py)]
+        cover = np.zeros((ny, nx), dtype=np.int32)
+        for r, (r0, nr, c0, nc) in enumerate(tiles):
+            cover[r0:r0 + nr, c0:c0 + nc] += 1
+            assert (r0, nr) == heatb200.slab_partition(ny, py, r // px) and (c0, nc) == heatb200.slab_partition(nx, px, r % px)
+        assert (cover == 1).all()
+    with pytest.raises(heatb200.HeatError):
+        tile_partition(nx, ny, 2, 2, 4)
+    # argument checks that need no GPU: tblock outside {0,1,2,4} is refused in one place, before any device work
+    cfg = _lib.HeatConfig()
+    cfg.struct_size = C.sizeof(_lib.HeatConfig)
+    cfg.nx = cfg.ny = 64
+    cfg.nranks = 1
+    h = C.c_void_p()
+    for bad in (3, 5, 8, -1):
+        cfg.tblock = bad
+        assert heatb200.lib().heat_init(C.byref(h), C.byref(cfg), None) == _lib.ERR_INVALID
+        assert b"tblock" in heatb200.lib().heat_last_error()
 
 
 def test_slab_partition():
