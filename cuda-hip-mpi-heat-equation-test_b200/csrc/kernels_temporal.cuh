@@ -33,8 +33,11 @@ template <typename T, int K> struct TemporalGeom {
     static constexpr int HX = (K + V - 1) / V * V;       // halo columns each side (vector aligned)
 };
 
+#ifndef HEAT_TEMP_MINB
+#define HEAT_TEMP_MINB 1
+#endif
 template <typename T, int ORDER, bool FMA, int K, int M>
-__global__ void __launch_bounds__(kTempWarps * 32)
+__global__ void __launch_bounds__(kTempWarps * 32, HEAT_TEMP_MINB)
 heat_temporal_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ dst, int nx, long pitch,
                      int y_begin, int y_end, int seg_rows, int nstrips, int nitems, int ybc0, int ybc1,
                      T rx, T ry, int pdl_early, int kflags, T* __restrict__ dst2, int shift2) {
@@ -191,6 +194,7 @@ struct TemporalState {
 inline int temporal_setup(TemporalState& st, void* const buf[2], bool f32, int rows, long pitch, int k,
                           std::string& err) {
     const int V = f32 ? 4 : 2;
+    // cells per lane = M * V
     const int M = 2;
     for (int b = 0; b < 2; ++b) {
         int rc = tma_make_map(&st.map[b], buf[b], f32, pitch, rows, 32 * M * V, kTempRS, err);
@@ -202,12 +206,11 @@ inline int temporal_setup(TemporalState& st, void* const buf[2], bool f32, int r
     return 0;
 }
 
-template <typename T, int ORDER, bool FMA, int K>
-inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* dst, int nx, long pitch, int yb,
-                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags,
-                                        T* dst2 = nullptr, int shift2 = 0) {
+template <typename T, int ORDER, bool FMA, int K, int M>
+inline cudaError_t launch_temporal_rows_m(const TemporalState& st, int which, T* dst, int nx, long pitch, int yb,
+                                          int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags,
+                                          T* dst2, int shift2) {
     constexpr int V = Pack<T>::V;
-    constexpr int M = 2;
     constexpr int WIN = 32 * M * V, HX = TemporalGeom<T, K>::HX, WOUT = WIN - 2 * HX;
     constexpr size_t smem = (size_t)kTempWarps * kTempStages * kTempRS * WIN * sizeof(T) +
                             (size_t)kTempWarps * kTempStages * sizeof(uint64_t);
@@ -224,7 +227,7 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
         // fp64 k=2: 1024-row segments 641 GLUPS, 44 -> 790, 14 -> 856, 11 -> 869, 8 -> 796; profiles/README.md, round 2) — but every
         // segment recomputes 2K rows of pipeline fill, so the best length grows with K: k=4 fp64 peaks at ~160 rows
         // (1492 GLUPS), fp32 at ~88.  That needs a grid of several waves; smaller grids keep whole waves instead.
-        const int resident = sm_count * 12;
+        const int resident = sm_count * (M == 1 ? 20 : 12);
         const int pref = K == 1 ? 14 : K == 2 ? (sizeof(T) == 8 ? 11 : 14) : (sizeof(T) == 8 ? 160 : 88);
         if ((long)nstrips * ((rows + pref - 1) / pref) >= 3L * resident) seg = pref;
         // Otherwise prefer a whole number of waves (3, 2 or 1) with segments long enough that the 2K re-read rows
@@ -248,6 +251,15 @@ inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* d
     const int pdl_early = grid >= 2 * sm_count * 4 ? 1 : 0;
     return launch_pdl(k, dim3(grid), dim3(kTempWarps * 32), smem, s, sweep_tail_window(dst, pitch, yb, ye, kflags), st.map[which], dst, nx, pitch, yb, ye, seg,
                       nstrips, nitems, ybc0, ybc1, rx, ry, pdl_early, kflags, dst2, shift2);
+}
+
+template <typename T, int ORDER, bool FMA, int K>
+inline cudaError_t launch_temporal_rows(const TemporalState& st, int which, T* dst, int nx, long pitch, int yb,
+                                        int ye, int ybc0, int ybc1, T rx, T ry, int sm_count, cudaStream_t s, int kflags,
+                                        T* dst2 = nullptr, int shift2 = 0) {
+    // M = 1 (half the registers per level, twice the warps, narrower strips) was measured and rejected: 16384^2
+    // fp64 k=4 1326 vs 1492 GLUPS, fp32 k=4 2414 vs 2520, k=2 796 vs 869 (profiles/r02_sweep_temporal_m.txt)
+    return launch_temporal_rows_m<T, ORDER, FMA, K, 2>(st, which, dst, nx, pitch, yb, ye, ybc0, ybc1, rx, ry, sm_count, s, kflags, dst2, shift2);
 }
 
 }  // namespace heat

@@ -145,6 +145,24 @@ def main():
                 print("tiles %dx%d case %d %s" % (px, world // px, ci, "ok" if int(t.item()) == 0 else "FAIL"), " ", flush=True)
                 if int(t.item()):
                     failures.append(("tiles", px, ci, int(t.item())))
+    # the MPI programs' own deck (fortran/mpi+cuda/input.dat: 100 0.25 0.05 2.0 10 1) through heatb200.mpi_deck: every rank
+    # writes its solnNNNNN.dat; stitched together they are, value for value, the field the reference's HIP kernels
+    # produce for that deck (tests/golden/hip_slabs_n100.npz)
+    import tempfile
+    from heatb200 import io as hio, mpi_deck
+    tmp = [tempfile.mkdtemp(prefix="heat_deck_") if rank == 0 else None]
+    dist.broadcast_object_list(tmp, 0)
+    deck, mine, _ = mpi_deck.run("100 0.25 0.05 2.0 10 1", tmp[0], ghost=2)
+    dist.barrier()
+    if rank == 0:
+        gold = np.load(os.path.join(ROOT, "tests", "golden", "hip_slabs_n100.npz"))["P1_rank0"][1:-1, 1:-1]
+        parts = [hio.read_dump(os.path.join(tmp[0], hio.rank_dump_name(r))) for r in range(world)]
+        glued = np.concatenate([p[2] for p in parts], axis=0)
+        ys = np.concatenate([p[1] for p in parts])
+        ok = glued.shape == gold.shape and np.array_equal(glued, gold) and np.array_equal(ys, parts[0][0])
+        print("mpi deck dumps %s" % ("ok" if ok else "FAIL"), " ", flush=True)
+        if not ok:
+            failures.append(("mpi_deck", glued.shape, gold.shape))
     flag = torch.tensor([len(failures)], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()

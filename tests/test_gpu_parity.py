@@ -280,6 +280,22 @@ def test_shipped_input_decks(deck_text, y_hi):
         assert_bit_equal(heatb200.march(u0, deck.ntime, r, kernel=kernel), want)
 
 
+def test_mpi_deck_dropin_single_rank(golden, tmp_path):
+    """heatb200.mpi_deck on one GPU with the MPI programs' shipped deck: the interior equals what the reference's
+    HIP kernels produce (golden), and soln00000.dat holds it with the reference's coordinates (heat.F90:136,277-288)."""
+    from heatb200 import io as hio, mpi_deck
+    deck, interior, _ = mpi_deck.run("100 0.25 0.05 2.0 10 1", str(tmp_path))
+    gold = golden("hip_slabs_n100.npz")["P1_rank0"]
+    assert deck.soln == 1 and interior.shape == (100, 100)
+    assert_bit_equal(interior, np.ascontiguousarray(gold[1:-1, 1:-1]))
+    x, y, T = hio.read_dump(str(tmp_path / "soln00000.dat"))
+    delta = ho.derive_fortran(100, 0.25, 0.05, 2.0)[0]
+    assert np.array_equal(T, interior) and np.array_equal(x, np.arange(100) * delta) and np.array_equal(y, x)
+    # soln = 0 (fortran/hip/input.dat) writes nothing
+    mpi_deck.run("64 0.25 0.05 1.0 5 0", str(tmp_path / "none"))
+    assert not (tmp_path / "none").exists()
+
+
 def test_cuda_dropin_small():
     from heatb200 import cuda
     cuda.configure(n=256, nt_=19, hat=True)
