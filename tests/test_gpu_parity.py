@@ -489,6 +489,32 @@ def test_job_pipeline_matches_blocking_calls(shape, dtype, k):
             s.submit(ins[0][:-1], 1, outs[0])
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_guard_bands_are_never_written_and_never_feed_a_result(dtype):
+    """Our own memory check (compute-sanitizer is not available on this pool): the two field buffers are views into
+    larger caller-owned allocations whose surrounding rows AND whose pitch padding are filled with NaN.  After a
+    march with every kernel the guard rows must still hold that bit pattern (no out-of-bounds write), the result
+    must equal the oracle bit for bit (so no NaN from a guard row or from the padding was ever used for an updated
+    cell), and the padding columns inside the rows may only have been rewritten with what they held."""
+    import torch
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    G = 8                                               # guard rows above and below each buffer
+    for (ny, nx, pitch) in [(70, 130, 144), (131, 1000, 1008), (300, 257, 272), (40, 64, 64)]:
+        u0 = rand_field((ny, nx), dtype, seed=nx)
+        want = ho.march(u0, 9, 0, dtype(R100))
+        for kernel, k in [("simple", 1), ("stream", 1), ("tma", 1), ("wtma", 1), ("tma", 2), ("tma", 4), ("persist", 1)]:
+            bigs = [torch.full((ny + 2 * G, pitch), float("nan"), dtype=tdt, device="cuda") for _ in range(2)]
+            bufs = tuple(b[G:G + ny] for b in bigs)
+            with heatb200.HeatSolver(u0, float(dtype(R100)), buffers=bufs, kernel=kernel, tblock=k) as s:
+                s.step(9)
+                got = s.gather()
+            assert_bit_equal(got, want)
+            for b in bigs:
+                assert bool(torch.isnan(b[:G]).all()) and bool(torch.isnan(b[G + ny:]).all()), (kernel, k, ny, nx, "guard rows written")
+                if pitch > nx:
+                    assert bool(torch.isnan(b[G:G + ny, nx:]).all()), (kernel, k, ny, nx, "pitch padding changed")
+
+
 def test_checksum_deterministic_and_close():
     u0 = rand_field((300, 500), seed=4)
     with heatb200.HeatSolver(u0, R100) as s:

@@ -64,11 +64,29 @@ try:
     raise SystemExit("short slab accepted")
 except ValueError:
     pass
+# 3b. 2-D tiles: my_tile agrees with the library's partition, the two ranks' tiles of a 2 x 1 cut tile the field,
+#     and a tile of the wrong shape is refused before any GPU work
+t0 = hd.my_tile(nx, ny, 2)
+assert t0 == heatb200.solver.tile_partition(nx, ny, 2, 1, rank) and t0[0] == 0 and t0[1] == ny
+tiles = [None] * world
+dist.all_gather_object(tiles, t0)
+assert tiles[0][2] == 0 and tiles[0][2] + tiles[0][3] == tiles[1][2] and tiles[1][2] + tiles[1][3] == nx
+full = ic.hat_fortran(nx, 2.0, delta)
+try:
+    hd.tile_solver(full[:, t0[2]:t0[2] + t0[3] - 1], nx, ny, 2, 0.25, nccl_id=got)
+    raise SystemExit("short tile accepted")
+except ValueError:
+    pass
 # 4. with no GPU the collective init fails loudly on every rank — no CPU fallback
 if not torch.cuda.is_available():
     try:
         hd.slab_solver(mine, ny, 0.25, nccl_id=got, ghost=2, overlap=True)
         raise SystemExit("heat_init succeeded without a GPU")
+    except heatb200.HeatError as e:
+        assert e.code == _lib.ERR_CUDA, e
+    try:
+        hd.tile_solver(np.ascontiguousarray(full[:, t0[2]:t0[2] + t0[3]]), nx, ny, 2, 0.25, nccl_id=got, ghost=2)
+        raise SystemExit("tile_solver succeeded without a GPU")
     except heatb200.HeatError as e:
         assert e.code == _lib.ERR_CUDA, e
 dist.barrier()
