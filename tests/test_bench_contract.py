@@ -1,4 +1,4 @@
-"""CPU: the bench JSON contract, checked on the lines committed under profiles/ (produced on a B200 by bench.py)."""
+"""CPU: the bench JSON contract, checked on the lines committed under profiles/ (produced on B200s by bench.py)."""
 import json
 import os
 
@@ -14,41 +14,53 @@ def load(name):
 
 
 def test_default_line_has_every_contract_key():
-    d = load("r01_bench_final_default.json")
+    d = load("r02_bench_default_cfg3.json")
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks"):
         assert k in d, k
     assert d["unit"] == "GLUPS" and d["higher_is_better"] is True and d["vs_baseline"] is None
     assert d["dtype"] == "f64" and d["data"] == "synthetic" and d["n_gpus"] == 1 and d["warmup"] >= 3
-    assert "workload" in d["config"] and "model" not in d["config"] and "l2" in d["config"]
+    c = d["config"]
+    assert c["workload"].startswith("cfg3") and c["nx"] == 16384 == c["ny_global"] and c["timesteps_per_step"] == 500
+    assert "model" not in c and "l2" in c and c["tblock"] == 1 and c["fmad"] is False
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
-    assert r["traffic"] is None or r["traffic"] > 0
-    c = d["cpu_baseline"]
-    assert c["kind"] in ("port", "reference") and c["cores"] >= 1 and c["value"] > 0 and c["sample"]
+    assert r["frac"] >= 0.85                                      # the north-star target on this very configuration
+    assert r["traffic"] == r["ncu"]["bytes"] and 0.95 < r["traffic"] / r["algorithmic_bytes_per_launch"] < 1.05
+    assert os.path.isfile(os.path.join(ROOT, r["ncu"]["source"]))
+    cb = d["cpu_baseline"]
+    assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and cb["value"] > 0 and cb["sample"]
     e = d["e2e"]
-    assert e["h2d_bytes_per_step"] == 4096 * 4096 * 8 == e["d2h_bytes_per_step"] and 0 < e["value"] < d["value"]
-    assert d["gpu_launches"] == d["steps"] * d["config"]["timesteps_per_step"]
+    assert e["h2d_bytes_per_step"] == 16384 * 16384 * 8 == e["d2h_bytes_per_step"] and 0 < e["value"] < d["value"]
+    assert e["steps"] == d["steps"] and 0 < e["serial"]["value"] < e["value"]
+    assert d["gpu_launches"] == d["steps"] * c["timesteps_per_step"]
     assert set(d["clocks"]) >= {"sm_mhz", "sm_max_mhz", "reasons"}
     bad = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
     assert not bad & set(d["clocks"]["reasons"])
     # value is consistent with its own timing: interior updates / time
-    lups = (4096 - 2) ** 2 * d["config"]["timesteps_per_step"]
+    lups = (16384 - 2) ** 2 * c["timesteps_per_step"]
     assert abs(d["value"] - lups / (d["ms_per_step"] * 1e-3) / 1e9) / d["value"] < 1e-6
 
 
-def test_reference_line():
-    d = load("r01_bench_final_reference.json")
+def test_reference_line_matches_the_gpu_arm_config():
+    d = load("r02_bench_reference_cfg3.json")
     assert d["impl"] == "reference" and d["unit"] == "GLUPS" and d["gpu_launches"] == 0
     assert d["e2e"] == {"value": d["value"], "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["cpu_baseline"]["value"] == d["value"] and d["cpu_baseline"]["kind"] == "port"
+    assert d["cpu_baseline"]["cores"] > 1                         # OpenMP threads set explicitly, whatever the launcher exported
+    assert d["config"] == load("r02_bench_default_cfg3.json")["config"]
 
 
-@pytest.mark.parametrize("name,n", [("r01_bench_n2_cfg2_final.json", 2), ("r01_bench_n4_cfg2_final.json", 4),
-                                    ("r01_bench_n8_cfg2_final.json", 8)])
-def test_multi_gpu_lines(name, n):
-    d = load(name)
-    assert d["n_gpus"] == n and d["scaling"] == "weak" and d["config"]["ny_global"] == 4096 * n
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_strong_scaling_lines_carry_parity(n):
+    d = load("r02_bench_n%d_cfg4.json" % n)
+    assert d["n_gpus"] == n and d["scaling"] == "strong" and d["config"]["ny_global"] == 32768 == d["config"]["nx"]
+    assert d["config"]["workload"].startswith("cfg4")
     assert "halo" in d and d["halo"]["exchanges"] > 0
-    one = load("r01_bench_n1_cfg2_final.json")["value"]
-    assert 0.9 < d["value"] / (n * one) <= 1.02          # weak-scaling efficiency measured in round 1
+    p = d["parity"]
+    assert p["ok"] is True and p["cases"] == 2
+    assert all(c["equals_1gpu"] and c["band_equals_cpu_oracle"] for c in p["detail"])
+    one = load("r02_bench_n1_cfg4.json")
+    assert one["scaling"] == "strong" and one["config"]["workload"].startswith("cfg4")
+    assert 0.9 < d["value"] / (n * one["value"]) <= 1.02         # strong-scaling efficiency measured in round 2
+    assert d["roofline"]["traffic"] is None                       # no single-GPU ncu figure pasted onto a multi-GPU line
