@@ -279,6 +279,28 @@ __global__ void heat_signal_kernel(uint32_t* a, uint32_t* b, uint32_t v) {
     __threadfence_system();
 }
 
+// Signal and wait in ONE 1-thread kernel: store the epoch into the neighbours' flags, then spin (ld.acquire.sys) until
+// both neighbours have stored it into ours.  It reacts within a memory round trip where a stream-ordered
+// cuStreamWaitValue32 is polled by the front end; it occupies one CTA slot while it waits, and it cannot deadlock: what
+// it waits for is stored by a kernel on ANOTHER GPU, whose progress never depends on this GPU's SMs.
+__global__ void heat_signal_wait_kernel(uint32_t* sig_a, uint32_t* sig_b, const uint32_t* wait_a, const uint32_t* wait_b, uint32_t v) {
+    if (sig_a) *reinterpret_cast<volatile uint32_t*>(sig_a) = v;
+    if (sig_b) *reinterpret_cast<volatile uint32_t*>(sig_b) = v;
+    __threadfence_system();
+    for (const uint32_t* w : {wait_a, wait_b}) {
+        if (!w) continue;
+        uint32_t got;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(w) : "memory");
+        } while ((int32_t)(got - v) < 0);
+    }
+}
+
+static bool peer_wait_in_kernel() {      // HEAT_PEER_WAIT=stream selects cuStreamWaitValue32 instead
+    static const bool on = [] { const char* v = getenv("HEAT_PEER_WAIT"); return !(v && v[0] == 's'); }();
+    return on;
+}
+
 typedef CUresult (*PFN_streamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 static PFN_streamWaitValue32 get_wait_value32() {
     static PFN_streamWaitValue32 fn = [] {
@@ -297,6 +319,12 @@ static int peer_handshake(heat_handle* h, int phase, uint32_t epoch, cudaStream_
     PFN_streamWaitValue32 wait32 = get_wait_value32();
     if (!wait32) return fail(HEAT_ERR_UNSUPPORTED, "peer halo: cuStreamWaitValue32 is not available from this driver");
     const bool up = h->cfg.rank > 0, down = h->cfg.rank + 1 < h->cfg.nranks;
+    if (peer_wait_in_kernel()) {
+        heat_signal_wait_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 2 * phase + 1 : nullptr, down ? h->down_flags + 2 * phase : nullptr,
+                                                up ? h->d_flags + 2 * phase : nullptr, down ? h->d_flags + 2 * phase + 1 : nullptr, epoch);
+        CUDA_TRY(cudaGetLastError());
+        return HEAT_OK;
+    }
     // I am the up neighbour's "down" and the down neighbour's "up"
     heat_signal_kernel<<<1, 1, 0, s>>>(up ? h->up_flags + 2 * phase + 1 : nullptr, down ? h->down_flags + 2 * phase : nullptr, epoch);
     CUDA_TRY(cudaGetLastError());
@@ -485,7 +513,7 @@ static int env_int(const char* name, int dflt) {
 extern "C" {
 
 const char* heat_last_error(void) { return g_err.c_str(); }
-const char* heat_version(void) { return "heat_b200 0.1 (sm_100a)"; }
+const char* heat_version(void) { return "heat_b200 0.2 (sm_100a)"; }
 
 int heat_slab_partition(int ny, int nranks, int rank, int* row0, int* nrows) {
     if (ny < 1 || nranks < 1 || rank < 0 || rank >= nranks || !row0 || !nrows)
@@ -657,9 +685,7 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     }
     h->gl = (h->px > 1 && h->rxi > 0) ? h->g : 0;
     h->gr = (h->px > 1 && h->rxi + 1 < h->px) ? h->g : 0;
-    h->nx = h->ncols + h->gl + h->gr;
-    const bool has_rows_above_below = h->py > 1;
-    if (!has_rows_above_below && cfg->nranks > 1) { /* px x 1: ghost rows are allocated but never exchanged */ }
+    h->nx = h->ncols + h->gl + h->gr;          // (px x 1 keeps its g ghost rows allocated; they are simply never exchanged)
     if (h->g % h->tblock != 0 && cfg->nranks > 1) {
         delete h;
         return fail(HEAT_ERR_INVALID, "heat_init: ghost depth %d must be a multiple of tblock %d", h->g, h->tblock);
