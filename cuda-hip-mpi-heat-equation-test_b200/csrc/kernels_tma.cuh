@@ -29,9 +29,17 @@ struct TmaState {
     int box_w = 0, box_h = 0;
 };
 
+// Stage shape (compile-time knobs).  Measured at 16384^2 fp64 with 46-row segments: 16 rows x 4 stages 432.6 GLUPS,
+// 8 x 8 432.8 (fp32 852 vs 858), 8 x 4 425.8, 32 x 2 281.1 — the kernel sits at its DRAM ceiling, the default stays.
+#ifndef HEAT_TMA_BY
+#define HEAT_TMA_BY 16
+#endif
+#ifndef HEAT_TMA_STAGES
+#define HEAT_TMA_STAGES 4
+#endif
 constexpr int kTmaBX = 128;      // strip width in cells
-constexpr int kTmaBY = 16;       // rows per stage
-constexpr int kTmaStages = 4;
+constexpr int kTmaBY = HEAT_TMA_BY;       // rows per stage
+constexpr int kTmaStages = HEAT_TMA_STAGES;
 constexpr int kTmaThreads = 256;
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) {
@@ -405,10 +413,10 @@ inline cudaError_t launch_tma_rows(const TmaState& st, int which, T* dst, int nx
     // field row band by row band: DRAM sees two compact streams (one read, one write) instead of ~13 scattered ones,
     // the two halo rows a segment shares with its neighbours are L2 hits, and the tail of the grid is short.  Measured
     // on B200 at 16384^2 fp64 (profiles/README.md, round 2): 1264-row segments 387 GLUPS, 94 -> 423, 46 -> 433,
-    // 30 -> 431, 16 -> 292 (per-CTA prologue dominates).  46 = 3 stages of 16 input rows exactly (46 + 2 halo rows).
+    // 30 -> 431, 16 -> 292 (per-CTA prologue dominates).  46 + 2 halo rows = 48 input rows = a whole number of stages.
     int seg = 0;
     if (const char* v = getenv("HEAT_TMA_SEG")) seg = atoi(v);
-    if (seg <= 0) seg = 3 * kTmaBY - 2;
+    if (seg <= 0) seg = 48 - 2;
     (void)sm_count;
     seg = std::min(seg, rows);
     const int gy = (rows + seg - 1) / seg;
