@@ -458,7 +458,11 @@ def main():
                 # `peak` is the pool's measured copy bandwidth (torch b.copy_(a)); it is not the ceiling of the HBM
                 # interface — this kernel's read and write streams are more compact than a flat copy's and pass it.
                 # Against the interface rate ncu reports its DRAM throughput against (8.18 TB/s):
-                "frac_of_hbm_interface_8180": achieved / 8180.0}
+                "frac_of_hbm_interface_8180": achieved / 8180.0,
+                "note": "frac = achieved / peak with peak = the pool's measured torch copy bandwidth; a value above 1 means this "
+                        "kernel moves its algorithmic bytes faster than that copy does, not that bytes were skipped: see `traffic` "
+                        "(ncu DRAM bytes per launch) next to algorithmic_bytes_per_launch and ncu.dram_pct (share of the HBM "
+                        "interface rate)"}
     if traffic:
         # what actually crossed the HBM pins per launch (ncu) over the same launch time: below `achieved` when part
         # of a step is served by the 126 MB L2 (4096^2), above it when halo columns / rows are re-read
