@@ -296,6 +296,24 @@ def test_mpi_deck_dropin_single_rank(golden, tmp_path):
     assert not (tmp_path / "none").exists()
 
 
+@pytest.mark.parametrize("deck_text,variant,y_hi", [("100 0.25 0.05 2.0 1000", "cuda", 1.0), ("257, 2.5d-1 5.0D-2 2.0 30 /", "serial", 1.5)])
+def test_fortran_deck_dropin(deck_text, variant, y_hi, tmp_path):
+    """heatb200.fortran_deck = `program heat` of fortran/serial (and cuda_cuf / cuda_kernel): int.dat holds the hat IC,
+    soln.dat the field after ntime steps, both readable the way the reference's init.py / out.py read them."""
+    from heatb200 import fortran_deck, io as hio
+    deck, c, T = fortran_deck.run(deck_text, str(tmp_path), variant=variant)
+    n = deck.n
+    want = ho.fortran_serial(n, deck.sigma, deck.nu, deck.dom_len, deck.ntime, y_hi) if n <= 128 else \
+        c_oracle.march(ho.ic_fortran(n, deck.dom_len, y_hi), deck.ntime, 0, ho.derive_fortran(n, deck.sigma, deck.nu, deck.dom_len)[2])
+    assert_bit_equal(T, want)
+    x, y, T2 = hio.read_dump(str(tmp_path / "soln.dat"))
+    assert np.array_equal(T2, T) and np.array_equal(x, c) and np.array_equal(y, c)
+    _, _, T0 = hio.read_dump(str(tmp_path / "int.dat"))
+    assert_bit_equal(T0, ho.ic_fortran(n, deck.dom_len, y_hi))
+    X, Y, Z = ho.read_soln(str(tmp_path / "soln.dat"))               # out.py's parsing
+    assert np.array_equal(Z, T.T)
+
+
 def test_cuda_dropin_small():
     from heatb200 import cuda
     cuda.configure(n=256, nt_=19, hat=True)

@@ -202,3 +202,20 @@ def test_io_dump_roundtrip_and_rank_files(tmp_path):
         parts.append(hio.read_dump(f)[2])
     assert np.array_equal(np.concatenate(parts), T)
     assert abs(hio.checksum_host(T) - T.sum()) < 1e-9
+
+
+def test_deck_dropins_fail_loudly_without_gpu(tmp_path):
+    """The program-level drop-ins have no CPU path either: on a box without a GPU they raise, and write no result file."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a box without a GPU")
+    from heatb200 import fortran_deck, mpi_deck
+    with pytest.raises(heatb200.HeatError) as e:
+        fortran_deck.run("64 0.25 0.05 2.0 5", str(tmp_path / "f"))
+    assert e.value.code == _lib.ERR_CUDA
+    assert (tmp_path / "f" / "int.dat").exists() and not (tmp_path / "f" / "soln.dat").exists()
+    with pytest.raises(heatb200.HeatError) as e:
+        mpi_deck.run("64 0.25 0.05 2.0 5 1", str(tmp_path / "m"))
+    assert e.value.code == _lib.ERR_CUDA and not (tmp_path / "m").exists()
+    with pytest.raises(ValueError):
+        fortran_deck.run("64 0.25 0.05 2.0 5", str(tmp_path / "f"), variant="hip")
