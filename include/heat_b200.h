@@ -145,9 +145,12 @@ int heat_step(heat_handle* h, int nt);
  * ref: swap(), fortran/mpi+cuda/heat.F90:145-193; launch_send/recv1/recv2 heat_kernel.cpp:63-150. */
 int heat_halo_exchange(heat_handle* h);
 
-/* Peer-memory halo (HEAT_FLAG_PEER_HALO, one process per GPU on one NVLink node): instead of NCCL, each
- * rank's copy engine writes its edge rows straight into the neighbours' ghost rows, which are mapped here
- * through CUDA IPC; ordering uses flag words and stream-ordered waits only.  After heat_init every rank calls
+/* Peer-memory halo (HEAT_FLAG_PEER_HALO, one process per GPU on one NVLink node, row slabs only): instead of
+ * NCCL, the edge-strip stencil kernels store their result rows into the own buffer AND, as peer stores over
+ * NVLink, into the neighbours' ghost rows, which are mapped here through CUDA IPC (kernels without that second
+ * destination and the first ghost fill use the copy engines); ordering uses one flag word per direction, signalled
+ * and awaited by a 1-thread kernel on the exchange stream (HEAT_PEER_WAIT=stream: cuStreamWaitValue32 instead).
+ * After heat_init every rank calls
  * heat_peer_export(blob) (HEAT_PEER_BLOB_BYTES bytes), the host layer hands each rank the blobs of rank-1 and
  * rank+1 (NULL at the ends), and heat_peer_attach opens them (no cross-GPU wait: the ghosts are filled by the
  * first heat_step / heat_halo_exchange, which all ranks must then call).
