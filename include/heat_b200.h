@@ -149,7 +149,8 @@ int heat_halo_exchange(heat_handle* h);
  * NCCL, the edge-strip stencil kernels store their result rows into the own buffer AND, as peer stores over
  * NVLink, into the neighbours' ghost rows, which are mapped here through CUDA IPC (kernels without that second
  * destination and the first ghost fill use the copy engines); ordering uses one flag word per direction, signalled
- * and awaited by a 1-thread kernel on the exchange stream (HEAT_PEER_WAIT=stream: cuStreamWaitValue32 instead).
+ * by a 1-thread kernel and awaited with cuStreamWaitValue32 on the exchange stream (HEAT_PEER_WAIT=kernel: one
+ * kernel that signals and spins).
  * After heat_init every rank calls
  * heat_peer_export(blob) (HEAT_PEER_BLOB_BYTES bytes), the host layer hands each rank the blobs of rank-1 and
  * rank+1 (NULL at the ends), and heat_peer_attach opens them (no cross-GPU wait: the ghosts are filled by the
