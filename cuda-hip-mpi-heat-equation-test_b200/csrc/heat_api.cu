@@ -661,8 +661,9 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     h->stream_threads = env_int("HEAT_STREAM_THREADS", 0);
     h->px = cfg->ranks_x > 0 ? cfg->ranks_x : 1;
     if (cfg->nranks % h->px != 0) {
+        const int px = h->px;
         delete h;
-        return fail(HEAT_ERR_INVALID, "heat_init: ranks_x %d does not divide nranks %d", h->px, cfg->nranks);
+        return fail(HEAT_ERR_INVALID, "heat_init: ranks_x %d does not divide nranks %d", px, cfg->nranks);
     }
     h->py = cfg->nranks / h->px;
     h->rxi = cfg->rank % h->px;
@@ -673,9 +674,10 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     // judged on the THINNEST tile of the partition, not on this rank's: every rank then takes the same
     // decision and none is left waiting inside the collective calls below
     if ((h->py > 1 && h->ny / h->py < h->g) || (h->px > 1 && h->gnx / h->px < h->g)) {
+        const int px = h->px, py = h->py, g = h->g;
         delete h;
         return fail(HEAT_ERR_INVALID, "heat_init: the thinnest tile (%d rows x %d columns: %d x %d over %d x %d ranks) is thinner than ghost depth %d",
-                    cfg->ny / h->py, cfg->nx / h->px, cfg->ny, cfg->nx, h->py, h->px, h->g);
+                    cfg->ny / py, cfg->nx / px, cfg->ny, cfg->nx, py, px, g);
     }
     if (h->px > 1 && (cfg->flags & HEAT_FLAG_PEER_HALO)) {
         delete h;
@@ -689,8 +691,9 @@ int heat_init(heat_handle** out, const heat_config* cfg, const void* field) {
     h->gr = (h->px > 1 && h->rxi + 1 < h->px) ? h->g : 0;
     h->nx = h->ncols + h->gl + h->gr;          // (px x 1 keeps its g ghost rows allocated; they are simply never exchanged)
     if (h->g % h->tblock != 0 && cfg->nranks > 1) {
+        const int g = h->g, k = h->tblock;
         delete h;
-        return fail(HEAT_ERR_INVALID, "heat_init: ghost depth %d must be a multiple of tblock %d", h->g, h->tblock);
+        return fail(HEAT_ERR_INVALID, "heat_init: ghost depth %d must be a multiple of tblock %d", g, k);
     }
     h->lrows = h->nrows + 2 * h->g;
 

@@ -554,6 +554,17 @@ def test_error_paths():
     with heatb200.HeatSolver(u0, 0.25) as s:
         with pytest.raises(heatb200.HeatError):
             s.step(-1)
+    # decompositions every rank must refuse alike, before any collective (messages built from global values only)
+    kw = dict(nx=64, ny=17, dtype=np.float64, nranks=2, rank=0, skip_exchange=True)
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.HeatSolver(None, 0.25, ghost=9, **kw)                     # thinnest slab has 8 rows
+    assert e.value.code == _lib.ERR_INVALID and "thinnest" in str(e.value) and "ghost depth 9" in str(e.value)
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.HeatSolver(None, 0.25, ghost=3, tblock=2, **kw)
+    assert e.value.code == _lib.ERR_INVALID and "ghost depth 3 must be a multiple of tblock 2" in str(e.value)
+    with pytest.raises(heatb200.HeatError) as e:
+        heatb200.HeatSolver(None, 0.25, ghost=2, ranks_x=2, peer_halo=True, **kw)
+    assert e.value.code == _lib.ERR_UNSUPPORTED and "row slabs only" in str(e.value)
 
 
 def test_legacy_launcher_large_ghosted_array():
