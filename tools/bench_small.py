@@ -4,7 +4,6 @@
 """
 import os
 import sys
-import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "cuda-hip-mpi-heat-equation-test_b200"))

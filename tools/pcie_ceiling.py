@@ -6,7 +6,6 @@ and prints the per-GPU and aggregate GB/s.  Plain copies only: this is the machi
 """
 import json
 import os
-import sys
 
 import torch
 import torch.distributed as dist
