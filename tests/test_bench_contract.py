@@ -64,3 +64,39 @@ def test_strong_scaling_lines_carry_parity(n):
     assert one["scaling"] == "strong" and one["config"]["workload"].startswith("cfg4")
     assert 0.9 < d["value"] / (n * one["value"]) <= 1.02         # strong-scaling efficiency measured in round 2
     assert d["roofline"]["traffic"] is None                       # no single-GPU ncu figure pasted onto a multi-GPU line
+
+
+# ------------------------------------------------------------------ bench.py's own choices (no GPU needed)
+def _bench_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("heat_bench", os.path.join(ROOT, "bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_workload_choice_follows_the_box(monkeypatch):
+    b = _bench_module()
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "0")
+    assert b.choose_workload("auto", 1)[0] == "cfg3"                 # single-GPU box: the roofline workload
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "0,1,2,3,4,5,6,7")
+    assert b.choose_workload("auto", 1)[0] == "cfg4"                 # N = 1 of a sweep on a multi-GPU box: strong scaling
+    for n in (2, 4, 8):
+        assert b.choose_workload("auto", n)[0] == "cfg4"
+    assert b.choose_workload("cfg2", 8)[0] == "cfg2" and b.choose_workload("cfg5", 1)[0] == "cfg5"
+    assert b.WORKLOADS["cfg3"]["nx"] == 16384 and b.WORKLOADS["cfg3"]["timesteps"] == 500
+    assert b.WORKLOADS["cfg4"]["nx"] == 32768 and b.WORKLOADS["cfg4"]["scaling"] == "strong"
+
+
+def test_config_is_a_function_of_the_command_line_only():
+    """Both arms build `config` with workload_config from the same arguments, so the driver's same_config holds."""
+    import argparse
+    b = _bench_module()
+    args = argparse.Namespace(dtype="f64", tblock=1, fmad=False, field="hat", kernel="auto", ghost=32, no_overlap=False, halo="auto")
+    for name, world in (("cfg3", 1), ("cfg4", 1), ("cfg4", 8), ("cfg2", 4)):
+        wl = b.WORKLOADS[name]
+        c1 = b.workload_config(args, name, "why", wl, world)
+        c2 = b.workload_config(args, name, "why", dict(wl), world)
+        assert c1 == c2 and c1["workload"].startswith(name) and "l2" in c1 and "model" not in c1
+        assert c1["ny_global"] == (wl["ny"] * world if wl["scaling"] == "weak" else wl["ny"])
+        assert ("ghost 32" in c1["parallelism"]) == (world > 1)

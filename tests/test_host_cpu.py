@@ -219,3 +219,30 @@ def test_deck_dropins_fail_loudly_without_gpu(tmp_path):
     assert e.value.code == _lib.ERR_CUDA and not (tmp_path / "m").exists()
     with pytest.raises(ValueError):
         fortran_deck.run("64 0.25 0.05 2.0 5", str(tmp_path / "f"), variant="hip")
+
+
+def test_input_dat_parser_agrees_with_the_oracle_on_random_decks():
+    """Property test: the product's list-directed parser and the oracle's accept the same decks and return the same
+    values, whatever the separators, exponent letters, optional 6th field and record terminator."""
+    from hypothesis import given, settings, strategies as st
+
+    seps = st.sampled_from([" ", "  ", ",", " , ", "\n", "\t"])
+    expo = st.sampled_from(["e", "E", "d", "D"])
+
+    @settings(max_examples=200, deadline=None)
+    @given(n=st.integers(2, 200000), sigma=st.floats(1e-3, 1.0), nu=st.floats(1e-3, 10.0), L=st.floats(0.1, 100.0),
+           ntime=st.integers(0, 10**6), soln=st.one_of(st.none(), st.integers(0, 1)), sep=st.lists(seps, min_size=5, max_size=5),
+           ex=expo, slash=st.booleans())
+    def check(n, sigma, nu, L, ntime, soln, sep, ex, slash):
+        def f(v):
+            return ("%.17e" % v).replace("e", ex)
+        text = str(n) + sep[0] + f(sigma) + sep[1] + f(nu) + sep[2] + f(L) + sep[3] + str(ntime)
+        if soln is not None:
+            text += sep[4] + str(soln)
+        if slash:
+            text += " / trailing words 1 2 3"
+        d = config.parse_input_dat(text + "\n")
+        assert (d.n, d.sigma, d.nu, d.dom_len, d.ntime, d.soln) == ho.parse_input_dat(text) == (n, sigma, nu, L, ntime, soln)
+        assert d.derive() == ho.derive_fortran(n, sigma, nu, L)
+
+    check()
